@@ -138,3 +138,14 @@ def collide(type1, pos1, mat1, size1, type2, pos2, mat2, size2, margin=0.0):
     p1, m1, p2, m2 = f(pos1, 3), f(mat1, 9), f(pos2, 3), f(mat2, 9)
     n = a.lib.oracle_debug_collide(type1, _p(p1), _p(m1), _p(s1), type2, _p(p2), _p(m2), _p(s2), margin, _p(out), 16)
     return out[:n]
+
+
+def efc(sim: OracleSim, env=0):
+    """Constraint rows of one env (re-runs forward): returns J [nefc,nv] and a dict of per-row columns."""
+    L = abi().lib
+    L.oracle_debug_efc.restype = C.c_int
+    L.oracle_debug_efc.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+    J = np.zeros((500, sim.nv)); cols = np.zeros((500, 8))
+    n = L.oracle_debug_efc(sim.h, env, _p(J), _p(cols), 500)
+    keys = ["type", "aref", "R", "floss", "force", "pos", "margin", "diagApprox"]
+    return J[:n], {k: cols[:n, i] for i, k in enumerate(keys)}
