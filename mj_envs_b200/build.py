@@ -1,0 +1,32 @@
+"""Builds the CUDA library in-tree: mj_envs_b200/libadroit_b200.so (sm_100a only)."""
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "csrc", "adroit_b200.cu")
+LIB = os.path.join(HERE, "libadroit_b200.so")
+DEPS = [os.path.join(HERE, "csrc", f) for f in ("adroit_b200.cu", "geom.cuh", "model.cuh", "dynamics.cuh", "constraint.cuh", "task.cuh")]
+DEPS.append(os.path.join(HERE, "..", "include", "adroit_b200.h"))
+
+
+def nvcc():
+    for p in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
+        if p and (os.path.exists(p) or p == "nvcc"):
+            return p
+    return "nvcc"
+
+
+def build(force=False, verbose=False):
+    if not force and os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(d) for d in DEPS):
+        return LIB
+    cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
+           "-Xcompiler", "-fPIC", "-o", LIB, SRC]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    subprocess.check_call(cmd)
+    return LIB
+
+
+if __name__ == "__main__":
+    import sys
+    print(build(force="-f" in sys.argv, verbose="-v" in sys.argv))

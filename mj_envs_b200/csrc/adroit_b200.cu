@@ -1,0 +1,737 @@
+// adroit_b200.cu — kernels and the C ABI (include/adroit_b200.h) of the batched Adroit simulator for sm_100a.
+//
+// One warp advances one environment through a whole env.step(): action map -> frame_skip x mj_step ->
+// observation / reward / success -> (optional) auto-reset, in a single launch.  See DESIGN.md for the data layout and
+// the per-phase roofline; the reference call sites each entry point replaces are cited in include/adroit_b200.h.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/adroit_b200.h"
+#include "task.cuh"
+
+namespace adroit {
+
+enum { MODE_STEP = 0, MODE_RESET = 1, MODE_FORWARD = 2 };
+
+// ---------------------------------------------------------------- device pipeline
+template <typename T> __device__ void forward(Ctx<T>& c, const DState<T>& st, int debug) {
+  const DModel<T>& m = c.m;
+  const int nv = m.nv, lane = c.lane;
+  kinematics(c);
+  frames_and_inertia(c);
+  mass_matrix(c);
+  if (debug) {
+    int ntri = (nv * (nv + 1)) / 2;
+    for (int p = lane; p < ntri; p += 32) c.g[G_DBG_M + p] = c.s[O_M + p];
+  }
+  collision(c, st.overflow);
+  rne_bias(c);
+  const bool slip = m.noslip_iterations > 0;
+  smooth_dynamics(c, slip);
+  make_constraint(c, st.overflow);
+  newton(c);
+  T *qacc = c.v(V_QACC), *qfc = c.v(V_QFC);
+  if (slip) {
+    noslip(c);
+    constraint_force(c);
+    T* u = c.v(V_T1);
+    symv_packed(c.g + G_MINV, qfc, u, nv, lane);
+    __syncwarp();
+    for (int j = lane; j < nv; j += 32) qacc[j] = c.v(V_QAS)[j] + u[j];
+    __syncwarp();
+  }
+  T touch = touch_sensor(c);
+  cache_task_frames(c, touch);
+  if (lane == 0) { c.gi[GI_NCON] = c.ncon; c.gi[GI_NSIMPLE] = c.nsimple; }
+  if (debug) {
+    for (int j = lane; j < nv; j += 32) {
+      c.g[G_DBG_QFS + j] = c.v(V_QFS)[j];
+      c.g[G_DBG_QAS + j] = c.v(V_QAS)[j];
+      c.g[G_DBG_QACC + j] = qacc[j];
+      c.g[G_DBG_QFC + j] = qfc[j];
+    }
+    for (int i = lane; i < 3 * m.nbody; i += 32) c.g[G_DBG_XPOS + i] = c.s[O_XPOS + i];
+    for (int i = lane; i < 4 * m.nbody; i += 32) c.g[G_DBG_XQUAT + i] = c.s[O_XQUAT + i];
+    for (int i = lane; i < 6 * MAXCON; i += 32) c.g[G_DBG_EF + i] = c.s[O_EF + i];
+  }
+  __syncwarp();
+}
+
+template <typename T> DI bool warp_bad(const T* x, int n, int lane) {
+  bool bad = false;
+  for (int j = lane; j < n; j += 32) bad |= !(tabs(x[j]) < T(1e10));
+  return __any_sync(0xffffffffu, bad);
+}
+template <typename T> DI void zero_state(Ctx<T>& c) {
+  for (int j = c.lane; j < NVP; j += 32) { c.v(V_QPOS)[j] = 0; c.v(V_QVEL)[j] = 0; c.v(V_WARM)[j] = 0; }
+  __syncwarp();
+}
+
+// mj_step: forward + semi-implicit Euler with implicit joint damping
+template <typename T> __device__ void substep(Ctx<T>& c, const DState<T>& st, int debug) {
+  const DModel<T>& m = c.m;
+  const int nv = m.nv, lane = c.lane;
+  if (warp_bad(c.v(V_QPOS), nv, lane) || warp_bad(c.v(V_QVEL), nv, lane)) zero_state(c);  // mj_checkPos / mj_checkVel
+  forward(c, st, debug);
+  if (warp_bad(c.v(V_QACC), nv, lane)) {  // mj_checkAcc
+    zero_state(c);
+    forward(c, st, debug);
+  }
+  T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL), *warm = c.v(V_WARM), *qacc = c.v(V_QACC), *x = c.v(V_T1);
+  const T h = m.timestep;
+  if (m.any_damping) {
+    T *H = c.s + O_H, *M = c.s + O_M;
+    int ntri = (nv * (nv + 1)) / 2;
+    for (int p = lane; p < ntri; p += 32) H[p] = M[p];
+    __syncwarp();
+    for (int j = lane; j < nv; j += 32) {
+      H[tri(j, j)] += h * m.dof_damping[j];
+      x[j] = c.v(V_QFS)[j] + c.v(V_QFC)[j];
+    }
+    __syncwarp();
+    chol_packed(H, nv, lane);
+    chol_solve_packed(H, x, nv, lane);
+  } else {
+    for (int j = lane; j < nv; j += 32) x[j] = qacc[j];
+    __syncwarp();
+  }
+  for (int j = lane; j < nv; j += 32) {
+    T v = qvel[j] + h * x[j];
+    qvel[j] = v;
+    qpos[j] += h * v;
+    warm[j] = qacc[j];
+  }
+  __syncwarp();
+}
+
+template <typename T> __device__ void episode_finish(const DModel<T>& m, const DState<T>& st, int env) {
+  if (st.t[env] == 0) return;
+  int thr = m.task == T_PEN ? 20 : 25;  // evaluate_success: hammer_v0.py:167-175, pen_v0.py:180-188
+  double* a = st.acc + 4 * env;
+  a[0] += (double)st.ep_return[env];
+  a[1] += st.ep_goal[env] > 0;
+  a[2] += st.ep_goal[env] > thr;
+  a[3] += 1;
+}
+
+// reset_model (hammer_v0.py:106-132, door_v0.py:103-119, pen_v0.py:115-132, relocate_v0.py:85-103) + mj_forward
+template <typename T> __device__ void reset_env(Ctx<T>& c, const DState<T>& st, int env, int debug) {
+  const DModel<T>& m = c.m;
+  if (c.lane == 0) {
+    episode_finish(m, st, env);
+    T par[NPARP];
+    draw_params(m, st.seed, (unsigned long long)(st.env_off + env), (unsigned)st.episode[env], par);
+    for (int i = 0; i < m.npar; i++) c.s[O_PAR + i] = par[i];
+    st.episode[env] += 1;
+    st.t[env] = 0;
+    st.ep_return[env] = 0;
+    st.ep_goal[env] = 0;
+  }
+  for (int j = c.lane; j < NVP; j += 32) c.v(V_CTRL)[j] = 0;
+  zero_state(c);
+  forward(c, st, debug);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(WPB * 32) env_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, int mode, const float* __restrict__ action,
+                                                        const uint8_t* __restrict__ mask, float* obs, float* reward, uint8_t* done,
+                                                        uint8_t* goal, int debug) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int env = blockIdx.x * WPB + warp;
+  if (env >= st.n) return;
+  T* s = reinterpret_cast<T*>(smem_raw) + (size_t)warp * SM_T;
+  int* si = reinterpret_cast<int*>(smem_raw + (size_t)WPB * SM_T * sizeof(T)) + warp * SM_I;
+  Ctx<T> c(m, s, si, st.scratch + (size_t)env * G_TOTAL, st.iscratch + (size_t)env * GI_TOTAL, lane);
+  if (mode == MODE_RESET && mask && !mask[env]) return;
+
+  // stage the persistent state
+  for (int j = lane; j < NVP; j += 32) {
+    c.v(V_QPOS)[j] = st.qpos[(size_t)env * NVP + j];
+    c.v(V_QVEL)[j] = st.qvel[(size_t)env * NVP + j];
+    c.v(V_WARM)[j] = st.warm[(size_t)env * NVP + j];
+    c.v(V_CTRL)[j] = 0;
+  }
+  if (lane < NPARP) s[O_PAR + lane] = st.par[(size_t)env * NPARP + lane];
+  if (lane < NTF) s[O_TF + lane] = st.tf[(size_t)env * NTF + lane];
+  __syncwarp();
+
+  if (mode == MODE_RESET) {
+    reset_env(c, st, env, debug);
+  } else if (mode == MODE_FORWARD) {
+    forward(c, st, debug);
+  } else {
+    // action map: hammer_v0.py:55-59 (act_mid / act_rng :49-50)
+    for (int u = lane; u < m.nu; u += 32) {
+      T a = tclamp((T)action[(size_t)env * m.nu + u], T(-1), T(1));
+      T lo = m.act_ctrlrange[2 * u], hi = m.act_ctrlrange[2 * u + 1];
+      c.v(V_CTRL)[u] = T(0.5) * (lo + hi) + a * T(0.5) * (hi - lo);
+    }
+    __syncwarp();
+    for (int k = 0; k < m.frame_skip; k++) substep(c, st, debug);  // do_simulation
+    T r;
+    int g, dn;
+    task_reward(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, lane, r, g, dn);
+    int tnew = st.t[env] + 1;
+    bool trunc = (st.flags & ADROIT_AUTO_RESET) && tnew >= m.horizon;
+    bool reset_now = trunc || ((st.flags & ADROIT_AUTO_RESET) && (st.flags & ADROIT_RESET_ON_DONE) && dn);
+    if (lane == 0) {
+      st.t[env] = tnew;
+      st.ep_return[env] += r;
+      st.ep_goal[env] += g;
+      if (reward) reward[env] = (float)r;
+      if (goal) goal[env] = (uint8_t)g;
+      if (done) done[env] = (uint8_t)(dn || trunc);
+    }
+    __syncwarp();
+    if (reset_now) reset_env(c, st, env, debug);
+  }
+  if (obs) write_obs(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, obs + (size_t)env * m.obs_dim, lane);
+  for (int j = lane; j < NVP; j += 32) {
+    st.qpos[(size_t)env * NVP + j] = c.v(V_QPOS)[j];
+    st.qvel[(size_t)env * NVP + j] = c.v(V_QVEL)[j];
+    st.warm[(size_t)env * NVP + j] = c.v(V_WARM)[j];
+  }
+  if (lane < NPARP) st.par[(size_t)env * NPARP + lane] = s[O_PAR + lane];
+  if (lane < NTF) st.tf[(size_t)env * NTF + lane] = s[O_TF + lane];
+}
+
+template <typename T> __global__ void obs_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, float* obs) {
+  int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (env >= st.n) return;
+  write_obs(m, st.qpos + (size_t)env * NVP, st.qvel + (size_t)env * NVP, st.tf + (size_t)env * NTF, obs + (size_t)env * m.obs_dim, lane);
+}
+
+// [n][w] <-> padded [n][stride] conversions between the fp64 host staging buffer and the typed device arrays
+template <typename T> __global__ void pack_kernel(T* dst, const double* src, int n, int w, int stride) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * w) return;
+  dst[(size_t)(i / w) * stride + i % w] = (T)src[i];
+}
+template <typename T> __global__ void unpack_kernel(double* dst, const T* src, int n, int w, int stride, int offset) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * w) return;
+  dst[i] = (double)src[(size_t)(i / w) * stride + offset + i % w];
+}
+__global__ void reduce_kernel(const double* acc, const int* t, const int* ep_goal, const float* retf, const double* retd, int n, int thr,
+                              int flush, double* out4) {
+  __shared__ double sh[4][32];
+  double v[4] = {0, 0, 0, 0};
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+    for (int k = 0; k < 4; k++) v[k] += acc[4 * e + k];
+    if (flush && t[e] > 0) {
+      v[0] += retf ? (double)retf[e] : retd[e];
+      v[1] += ep_goal[e] > 0;
+      v[2] += ep_goal[e] > thr;
+      v[3] += 1;
+    }
+  }
+  for (int k = 0; k < 4; k++) v[k] = warp_sum(v[k]);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) for (int k = 0; k < 4; k++) sh[k][warp] = v[k];
+  __syncthreads();
+  if (warp == 0) {
+    for (int k = 0; k < 4; k++) {
+      double x = lane < (int)(blockDim.x >> 5) ? sh[k][lane] : 0.0;
+      x = warp_sum(x);
+      if (lane == 0) atomicAdd(out4 + k, x);
+    }
+  }
+}
+
+}  // namespace adroit
+
+// ================================================================ host side
+using namespace adroit;
+
+static thread_local char g_err[512];
+#define FAIL(...) do { snprintf(g_err, sizeof g_err, __VA_ARGS__); return 1; } while (0)
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) FAIL("%s failed: %s", #call, cudaGetErrorString(e_)); } while (0)
+
+namespace {
+
+struct Blob {
+  const unsigned char* b;
+  const void* find(const char* name, int want_dt, int* count) const {
+    uint64_t nf;
+    memcpy(&nf, b + 8, 8);
+    for (uint64_t i = 0; i < nf; i++) {
+      const unsigned char* e = b + 16 + 48 * i;
+      if (strncmp((const char*)e, name, 32) == 0) {
+        uint32_t dt, cnt;
+        uint64_t off;
+        memcpy(&dt, e + 32, 4); memcpy(&cnt, e + 36, 4); memcpy(&off, e + 40, 8);
+        if ((int)dt != want_dt) return nullptr;
+        if (count) *count = (int)cnt;
+        return b + off;
+      }
+    }
+    return nullptr;
+  }
+  std::vector<int> ints(const char* n) const {
+    int c = 0;
+    const int* p = (const int*)find(n, 0, &c);
+    if (!p) throw std::string("model blob misses int field ") + n;
+    return std::vector<int>(p, p + c);
+  }
+  std::vector<double> reals(const char* n) const {
+    int c = 0;
+    const double* p = (const double*)find(n, 1, &c);
+    if (!p) throw std::string("model blob misses real field ") + n;
+    return std::vector<double>(p, p + c);
+  }
+};
+
+void quat2mat_h(const double* q, double* R) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  R[0] = w * w + x * x - y * y - z * z; R[1] = 2 * (x * y - w * z); R[2] = 2 * (x * z + w * y);
+  R[3] = 2 * (x * y + w * z); R[4] = w * w - x * x + y * y - z * z; R[5] = 2 * (y * z - w * x);
+  R[6] = 2 * (x * z - w * y); R[7] = 2 * (y * z + w * x); R[8] = w * w - x * x - y * y + z * z;
+}
+
+// device arena holding every model table
+struct Arena {
+  std::vector<unsigned char> host;
+  unsigned char* dev = nullptr;
+  template <typename U> size_t put(const std::vector<U>& v) {
+    size_t off = (host.size() + 15) & ~size_t(15);
+    host.resize(off + v.size() * sizeof(U) + 16);
+    if (!v.empty()) memcpy(host.data() + off, v.data(), v.size() * sizeof(U));
+    return off;
+  }
+};
+template <typename T> std::vector<T> conv(const std::vector<double>& v) { return std::vector<T>(v.begin(), v.end()); }
+
+}  // namespace
+
+struct adroit_sim {
+  int n = 0, device = 0;
+  bool f64 = false;
+  uint32_t flags = 0;
+  int nv = 0, nu = 0, obs_dim = 0, npar = 0, horizon = 0, frame_skip = 0, nbody = 0, nsite = 0, task = 0;
+  Arena arena;
+  DModel<float> mf;
+  DModel<double> md;
+  DState<float> sf;
+  DState<double> sd;
+  std::vector<void*> allocs;
+  double* stage = nullptr;      // device fp64 staging buffer
+  size_t stage_len = 0;
+  float *d_action = nullptr, *d_obs = nullptr, *d_reward = nullptr;
+  uint8_t *d_done = nullptr, *d_goal = nullptr;
+  double* d_out4 = nullptr;
+  int64_t launches = 0;
+};
+
+namespace {
+
+template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
+  auto sizes = B.ints("sizes");
+  m.nv = sizes[0]; m.nbody = sizes[1]; m.ngeom = sizes[2]; m.nsite = sizes[3]; m.nu = sizes[4]; m.ntendon = sizes[5];
+  m.npair = sizes[6]; m.npar = sizes[7]; m.obs_dim = sizes[8]; m.frame_skip = sizes[9]; m.task = sizes[10]; m.horizon = sizes[11];
+  if (m.nv > 36 || m.nbody > NBP || m.ngeom > NGP || m.nsite > NSP || m.npar > NPARP || m.nu > NVP)
+    throw std::string("model exceeds the compiled capacity of the CUDA kernels");
+  auto body_parent = B.ints("body_parent"), jntadr = B.ints("body_jntadr"), jntnum = B.ints("body_jntnum");
+  auto depth = B.ints("body_depth");
+  int nb = m.nbody, maxd = 0;
+  for (int b = 0; b < nb; b++) maxd = depth[b] > maxd ? depth[b] : maxd;
+  m.nlevel = maxd + 1;
+  std::vector<int> level_start(m.nlevel + 1, 0), level_body, child_start(nb + 1, 0), child_list;
+  for (int L = 0; L <= maxd; L++) {
+    level_start[L] = (int)level_body.size();
+    for (int b = 0; b < nb; b++) if (depth[b] == L) level_body.push_back(b);
+  }
+  level_start[m.nlevel] = (int)level_body.size();
+  for (int p = 0; p < nb; p++) {
+    child_start[p] = (int)child_list.size();
+    for (int b = 1; b < nb; b++) if (body_parent[b] == p) child_list.push_back(b);
+  }
+  child_start[nb] = (int)child_list.size();
+  std::vector<unsigned long long> dofmask(nb, 0ull);
+  for (int b = 1; b < nb; b++) {
+    dofmask[b] = dofmask[body_parent[b]];
+    for (int k = 0; k < jntnum[b]; k++) dofmask[b] |= 1ull << (jntadr[b] + k);
+  }
+  auto iquat = B.reals("body_iquat"), gquat = B.reals("geom_quat");
+  std::vector<double> imat(9 * nb), gmat(9 * m.ngeom);
+  for (int b = 0; b < nb; b++) quat2mat_h(&iquat[4 * b], &imat[9 * b]);
+  for (int g = 0; g < m.ngeom; g++) quat2mat_h(&gquat[4 * g], &gmat[9 * g]);
+  auto act_dof = B.ints("act_dof");
+  for (size_t i = 0; i < act_dof.size(); i++)
+    for (size_t j = i + 1; j < act_dof.size(); j++)
+      if (act_dof[i] == act_dof[j]) throw std::string("two actuators on one dof are outside the Adroit subset");
+
+  struct Fix { size_t off; const void** slot; };
+  std::vector<Fix> fix;
+  auto PI = [&](const int*& slot, const std::vector<int>& v) { fix.push_back({A.put(v), (const void**)&slot}); };
+  auto PR = [&](const T*& slot, const std::vector<double>& v) { fix.push_back({A.put(conv<T>(v)), (const void**)&slot}); };
+  PI(m.body_parent, body_parent); PI(m.body_jntadr, jntadr); PI(m.body_jntnum, jntnum); PI(m.body_par, B.ints("body_par"));
+  PI(m.level_start, level_start); PI(m.level_body, level_body); PI(m.child_start, child_start); PI(m.child_list, child_list);
+  fix.push_back({A.put(dofmask), (const void**)&m.body_dofmask});
+  PR(m.body_pos, B.reals("body_pos")); PR(m.body_quat, B.reals("body_quat")); PR(m.body_ipos, B.reals("body_ipos"));
+  PR(m.body_imat, imat); PR(m.body_mass, B.reals("body_mass")); PR(m.body_inertia, B.reals("body_inertia"));
+  PR(m.body_invweight0, B.reals("body_invweight0"));
+  PI(m.jnt_type, B.ints("jnt_type")); PI(m.jnt_limited, B.ints("jnt_limited")); PI(m.dof_body, B.ints("dof_body"));
+  PI(m.dof_parent, B.ints("dof_parent"));
+  PR(m.jnt_pos, B.reals("jnt_pos")); PR(m.jnt_axis, B.reals("jnt_axis")); PR(m.jnt_range, B.reals("jnt_range"));
+  PR(m.jnt_margin, B.reals("jnt_margin")); PR(m.dof_damping, B.reals("dof_damping")); PR(m.dof_armature, B.reals("dof_armature"));
+  PR(m.dof_frictionloss, B.reals("dof_frictionloss")); PR(m.dof_invweight0, B.reals("dof_invweight0"));
+  PI(m.geom_type, B.ints("geom_type")); PI(m.geom_body, B.ints("geom_body"));
+  PR(m.geom_pos, B.reals("geom_pos")); PR(m.geom_mat, gmat); PR(m.geom_size, B.reals("geom_size")); PR(m.geom_rbound, B.reals("geom_rbound"));
+  PI(m.site_body, B.ints("site_body")); PI(m.site_par, B.ints("site_par")); PR(m.site_pos, B.reals("site_pos"));
+  PI(m.pair_geom, B.ints("pair_geom")); PI(m.pair_condim, B.ints("pair_condim"));
+  PR(m.pair_friction, B.reals("pair_friction")); PR(m.pair_margin, B.reals("pair_margin"));
+  PI(m.tendon_dof, B.ints("tendon_dof")); PI(m.tendon_limited, B.ints("tendon_limited"));
+  PR(m.tendon_coef, B.reals("tendon_coef")); PR(m.tendon_range, B.reals("tendon_range")); PR(m.tendon_margin, B.reals("tendon_margin"));
+  PR(m.tendon_invweight0, B.reals("tendon_invweight0"));
+  PI(m.act_dof, act_dof); PR(m.act_ctrlrange, B.reals("act_ctrlrange")); PR(m.act_gain, B.reals("act_gain")); PR(m.act_bias, B.reals("act_bias"));
+  // stash offsets; pointers are patched once the arena is on the device
+  for (auto& f : fix) *f.slot = (const void*)f.off;
+
+  auto ti = B.ints("task_int");
+  for (int i = 0; i < 16; i++) m.task_int[i] = ti[i];
+  auto par0 = B.reals("par0");
+  for (int i = 0; i < NPARP; i++) m.par0[i] = i < (int)par0.size() ? (T)par0[i] : T(0);
+  m.touch_site = B.ints("touch_site")[0];
+  auto ssz = B.reals("site_size");
+  for (int i = 0; i < 3; i++) m.touch_size[i] = m.touch_site >= 0 ? (T)ssz[3 * m.touch_site + i] : T(0);
+  auto o = B.reals("opt_real");
+  auto oi = B.ints("opt_int");
+  m.timestep = (T)o[0]; m.gravity[0] = (T)o[1]; m.gravity[1] = (T)o[2]; m.gravity[2] = (T)o[3];
+  m.tolerance = (T)o[4]; m.noslip_tolerance = (T)o[5]; m.impratio = (T)o[6]; m.solref[0] = (T)o[7]; m.solref[1] = (T)o[8];
+  for (int i = 0; i < 5; i++) m.solimp[i] = (T)o[9 + i];
+  m.mpr_tolerance = (T)o[14];
+  m.iterations = oi[0]; m.noslip_iterations = oi[1]; m.mpr_iterations = oi[2];
+  m.meaninertia = (T)B.reals("meaninertia")[0];
+  m.pen_len = m.tar_len = T(1);
+  if (m.task == T_PEN) {  // pen_v0.py:57-58: |object_top - object_bottom| (both sites sit on one body)
+    auto sp = B.reals("site_pos");
+    auto len = [&](int a, int b) {
+      double s = 0;
+      for (int i = 0; i < 3; i++) s += (sp[3 * a + i] - sp[3 * b + i]) * (sp[3 * a + i] - sp[3 * b + i]);
+      return std::sqrt(s);
+    };
+    m.pen_len = (T)len(ti[4], ti[5]);
+    m.tar_len = (T)len(ti[6], ti[7]);
+  }
+  auto damp = B.reals("dof_damping");
+  m.any_damping = 0;
+  for (double d : damp) m.any_damping |= d > 0;
+}
+
+template <typename T> void patch_model(DModel<T>& m, unsigned char* dev) {
+  // every pointer member currently holds an arena offset
+  const void** p = (const void**)&m.body_parent;
+  const void** end = (const void**)&m.task_int;
+  for (; p < end; p++) *p = (const void*)(dev + (size_t)*p);
+}
+
+template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
+  int n = s->n;
+  auto A = [&](void** p, size_t bytes) -> int {
+    CK(cudaMalloc(p, bytes));
+    CK(cudaMemset(*p, 0, bytes));
+    s->allocs.push_back(*p);
+    return 0;
+  };
+  st.n = n;
+  if (A((void**)&st.qpos, sizeof(T) * n * NVP) || A((void**)&st.qvel, sizeof(T) * n * NVP) || A((void**)&st.warm, sizeof(T) * n * NVP) ||
+      A((void**)&st.par, sizeof(T) * n * NPARP) || A((void**)&st.tf, sizeof(T) * n * NTF) ||
+      A((void**)&st.scratch, sizeof(T) * (size_t)n * G_TOTAL) || A((void**)&st.iscratch, sizeof(int) * (size_t)n * GI_TOTAL) ||
+      A((void**)&st.t, sizeof(int) * n) || A((void**)&st.episode, sizeof(int) * n) || A((void**)&st.ep_goal, sizeof(int) * n) ||
+      A((void**)&st.ep_return, sizeof(T) * n) || A((void**)&st.acc, sizeof(double) * 4 * n) ||
+      A((void**)&st.overflow, sizeof(unsigned long long) * 2))
+    return 1;
+  return 0;
+}
+
+template <typename T>
+int launch_env(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, const float* action, const uint8_t* mask, float* obs,
+               float* reward, uint8_t* done, uint8_t* goal, int debug, cudaStream_t stream) {
+  size_t smem = WPB * smem_per_warp<T>();
+  static thread_local bool configured_f = false, configured_d = false;
+  bool& configured = sizeof(T) == 4 ? configured_f : configured_d;
+  if (!configured) {
+    CK(cudaFuncSetAttribute(env_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  int blocks = (st.n + WPB - 1) / WPB;
+  env_kernel<T><<<blocks, WPB * 32, smem, stream>>>(m, st, mode, action, mask, obs, reward, done, goal, debug);
+  CK(cudaGetLastError());
+  s->launches++;
+  return 0;
+}
+
+int ensure_stage(adroit_sim* s, size_t n) {
+  if (s->stage_len >= n) return 0;
+  if (s->stage) cudaFree(s->stage);
+  CK(cudaMalloc((void**)&s->stage, n * sizeof(double)));
+  s->stage_len = n;
+  return 0;
+}
+
+int run(adroit_sim* s, int mode, const float* action, const uint8_t* mask, float* obs, float* reward, uint8_t* done, uint8_t* goal,
+        int debug, void* stream) {
+  CK(cudaSetDevice(s->device));
+  if (s->f64) return launch_env<double>(s, s->md, s->sd, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
+  return launch_env<float>(s, s->mf, s->sf, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
+}
+
+// host fp64 [n][w]  ->  device typed [n][stride]
+int upload_field(adroit_sim* s, const double* host, void* dev, int w, int stride, cudaStream_t st) {
+  size_t cnt = (size_t)s->n * w;
+  if (ensure_stage(s, cnt)) return 1;
+  CK(cudaMemcpyAsync(s->stage, host, cnt * sizeof(double), cudaMemcpyHostToDevice, st));
+  int thr = 256, blk = (int)((cnt + thr - 1) / thr);
+  if (s->f64) pack_kernel<double><<<blk, thr, 0, st>>>((double*)dev, s->stage, s->n, w, stride);
+  else pack_kernel<float><<<blk, thr, 0, st>>>((float*)dev, s->stage, s->n, w, stride);
+  CK(cudaGetLastError());
+  s->launches++;
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+int download_field(adroit_sim* s, double* host, const void* dev, int w, int stride, int offset, cudaStream_t st) {
+  size_t cnt = (size_t)s->n * w;
+  if (ensure_stage(s, cnt)) return 1;
+  int thr = 256, blk = (int)((cnt + thr - 1) / thr);
+  if (s->f64) unpack_kernel<double><<<blk, thr, 0, st>>>(s->stage, (const double*)dev, s->n, w, stride, offset);
+  else unpack_kernel<float><<<blk, thr, 0, st>>>(s->stage, (const float*)dev, s->n, w, stride, offset);
+  CK(cudaGetLastError());
+  s->launches++;
+  CK(cudaMemcpyAsync(host, s->stage, cnt * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+}  // namespace
+
+#define STF(field) (s->f64 ? (void*)s->sd.field : (void*)s->sf.field)
+
+extern "C" {
+
+const char* adroit_last_error(void) { return g_err; }
+
+int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int device_id, uint64_t seed, int64_t env_id_offset,
+                  uint32_t flags, adroit_sim** out) {
+  if (!model_blob || blob_len < 16 || memcmp(model_blob, "ADRB200\x01", 8) != 0) FAIL("bad model blob");
+  if (n_envs <= 0) FAIL("n_envs must be positive");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) FAIL("no CUDA device: the CUDA path has no CPU fallback");
+  if (device_id < 0 || device_id >= ndev) FAIL("device %d out of range (%d devices)", device_id, ndev);
+  CK(cudaSetDevice(device_id));
+  adroit_sim* s = new adroit_sim();
+  s->n = n_envs; s->device = device_id; s->flags = flags; s->f64 = (flags & ADROIT_F64) != 0;
+  Blob B{(const unsigned char*)model_blob};
+  try {
+    if (s->f64) fill_model(s->md, s->arena, B); else fill_model(s->mf, s->arena, B);
+  } catch (const std::string& e) {
+    delete s;
+    FAIL("%s", e.c_str());
+  }
+  if (cudaMalloc((void**)&s->arena.dev, s->arena.host.size()) != cudaSuccess) { delete s; FAIL("cudaMalloc(model) failed"); }
+  s->allocs.push_back(s->arena.dev);
+  CK(cudaMemcpy(s->arena.dev, s->arena.host.data(), s->arena.host.size(), cudaMemcpyHostToDevice));
+  int rc;
+  if (s->f64) {
+    patch_model(s->md, s->arena.dev);
+    rc = alloc_state(s, s->sd);
+    s->sd.seed = seed; s->sd.env_off = env_id_offset; s->sd.flags = flags;
+    s->nv = s->md.nv; s->nu = s->md.nu; s->obs_dim = s->md.obs_dim; s->npar = s->md.npar; s->horizon = s->md.horizon;
+    s->frame_skip = s->md.frame_skip; s->nbody = s->md.nbody; s->nsite = s->md.nsite; s->task = s->md.task;
+  } else {
+    patch_model(s->mf, s->arena.dev);
+    rc = alloc_state(s, s->sf);
+    s->sf.seed = seed; s->sf.env_off = env_id_offset; s->sf.flags = flags;
+    s->nv = s->mf.nv; s->nu = s->mf.nu; s->obs_dim = s->mf.obs_dim; s->npar = s->mf.npar; s->horizon = s->mf.horizon;
+    s->frame_skip = s->mf.frame_skip; s->nbody = s->mf.nbody; s->nsite = s->mf.nsite; s->task = s->mf.task;
+  }
+  if (rc) { adroit_destroy(s); return 1; }
+  // model-default parameters, then one forward so that frames / observations are defined before the first reset
+  std::vector<double> par((size_t)n_envs * s->npar);
+  for (int e = 0; e < n_envs; e++)
+    for (int i = 0; i < s->npar; i++) par[(size_t)e * s->npar + i] = s->f64 ? s->md.par0[i] : (double)s->mf.par0[i];
+  if (upload_field(s, par.data(), STF(par), s->npar, NPARP, 0)) { adroit_destroy(s); return 1; }
+  if (cudaMalloc((void**)&s->d_out4, 4 * sizeof(double)) != cudaSuccess) { adroit_destroy(s); FAIL("cudaMalloc failed"); }
+  s->allocs.push_back(s->d_out4);
+  if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr)) { adroit_destroy(s); return 1; }
+  if (cudaDeviceSynchronize() != cudaSuccess) { adroit_destroy(s); FAIL("initial forward failed: %s", cudaGetErrorString(cudaGetLastError())); }
+  *out = s;
+  return 0;
+}
+
+void adroit_destroy(adroit_sim* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  for (void* p : s->allocs) cudaFree(p);
+  if (s->stage) cudaFree(s->stage);
+  if (s->d_action) cudaFree(s->d_action);
+  if (s->d_obs) cudaFree(s->d_obs);
+  if (s->d_reward) cudaFree(s->d_reward);
+  if (s->d_done) cudaFree(s->d_done);
+  if (s->d_goal) cudaFree(s->d_goal);
+  delete s;
+}
+
+int adroit_sizes(const adroit_sim* s, int* o) {
+  o[0] = s->nv; o[1] = s->nu; o[2] = s->obs_dim; o[3] = s->npar; o[4] = s->horizon; o[5] = s->frame_skip; o[6] = s->nbody; o[7] = s->nsite;
+  return 0;
+}
+
+int adroit_reset(adroit_sim* s, const uint8_t* mask_dev, float* obs_dev, void* stream) {
+  return run(s, MODE_RESET, nullptr, mask_dev, obs_dev, nullptr, nullptr, nullptr, 0, stream);
+}
+
+int adroit_step(adroit_sim* s, const float* action_dev, float* obs_dev, float* reward_dev, uint8_t* done_dev, uint8_t* goal_dev, void* stream) {
+  if (!action_dev) FAIL("action is NULL");
+  return run(s, MODE_STEP, action_dev, nullptr, obs_dev, reward_dev, done_dev, goal_dev, 0, stream);
+}
+
+int adroit_step_host(adroit_sim* s, const float* action_host, float* obs_host, float* reward_host, uint8_t* done_host, uint8_t* goal_host,
+                     void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  size_t n = s->n;
+  if (!s->d_action) {
+    CK(cudaMalloc((void**)&s->d_action, n * s->nu * sizeof(float)));
+    CK(cudaMalloc((void**)&s->d_obs, n * s->obs_dim * sizeof(float)));
+    CK(cudaMalloc((void**)&s->d_reward, n * sizeof(float)));
+    CK(cudaMalloc((void**)&s->d_done, n));
+    CK(cudaMalloc((void**)&s->d_goal, n));
+  }
+  CK(cudaMemcpyAsync(s->d_action, action_host, n * s->nu * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (run(s, MODE_STEP, s->d_action, nullptr, s->d_obs, s->d_reward, s->d_done, s->d_goal, 0, stream)) return 1;
+  if (obs_host) CK(cudaMemcpyAsync(obs_host, s->d_obs, n * s->obs_dim * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (reward_host) CK(cudaMemcpyAsync(reward_host, s->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (done_host) CK(cudaMemcpyAsync(done_host, s->d_done, n, cudaMemcpyDeviceToHost, st));
+  if (goal_host) CK(cudaMemcpyAsync(goal_host, s->d_goal, n, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int adroit_get_obs(adroit_sim* s, float* obs_dev, void* stream) {
+  CK(cudaSetDevice(s->device));
+  int thr = 128, blk = (int)(((size_t)s->n * 32 + thr - 1) / thr);
+  if (s->f64) obs_kernel<double><<<blk, thr, 0, (cudaStream_t)stream>>>(s->md, s->sd, obs_dev);
+  else obs_kernel<float><<<blk, thr, 0, (cudaStream_t)stream>>>(s->mf, s->sf, obs_dev);
+  CK(cudaGetLastError());
+  s->launches++;
+  return 0;
+}
+
+int adroit_get_state(adroit_sim* s, double* qpos, double* qvel, double* par, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  if (qpos && download_field(s, qpos, STF(qpos), s->nv, NVP, 0, st)) return 1;
+  if (qvel && download_field(s, qvel, STF(qvel), s->nv, NVP, 0, st)) return 1;
+  if (par && download_field(s, par, STF(par), s->npar, NPARP, 0, st)) return 1;
+  return 0;
+}
+
+int adroit_set_state(adroit_sim* s, const double* qpos, const double* qvel, const double* par, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  if (qpos && upload_field(s, qpos, STF(qpos), s->nv, NVP, st)) return 1;
+  if (qvel && upload_field(s, qvel, STF(qvel), s->nv, NVP, st)) return 1;
+  if (par && upload_field(s, par, STF(par), s->npar, NPARP, st)) return 1;
+  if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int adroit_get_warmstart(adroit_sim* s, double* w, void* stream) {
+  CK(cudaSetDevice(s->device));
+  return download_field(s, w, STF(warm), s->nv, NVP, 0, (cudaStream_t)stream);
+}
+int adroit_set_warmstart(adroit_sim* s, const double* w, void* stream) {
+  CK(cudaSetDevice(s->device));
+  return upload_field(s, w, STF(warm), s->nv, NVP, (cudaStream_t)stream);
+}
+
+int adroit_get_frames(adroit_sim* s, double* bx, double* bq, double* sx, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  // frames are exported by a debug forward on the current state
+  if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
+  if (bx && download_field(s, bx, STF(scratch), 3 * s->nbody, G_TOTAL, G_DBG_XPOS, st)) return 1;
+  if (bq && download_field(s, bq, STF(scratch), 4 * s->nbody, G_TOTAL, G_DBG_XQUAT, st)) return 1;
+  if (sx && download_field(s, sx, STF(scratch), 3 * s->nsite, G_TOTAL, G_SPOS, st)) return 1;
+  return 0;
+}
+
+int adroit_get_solver(adroit_sim* s, double* qacc, int32_t* ncon, int32_t* nefc, double* touch, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
+  if (qacc && download_field(s, qacc, STF(scratch), s->nv, G_TOTAL, G_DBG_QACC, st)) return 1;
+  if (touch && download_field(s, touch, STF(tf), 1, NTF, 19, st)) return 1;
+  if (ncon || nefc) {
+    std::vector<int> gi((size_t)s->n * GI_TOTAL);
+    CK(cudaMemcpyAsync(gi.data(), s->f64 ? s->sd.iscratch : s->sf.iscratch, gi.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (int e = 0; e < s->n; e++) {
+      const int* g = &gi[(size_t)e * GI_TOTAL];
+      if (ncon) ncon[e] = g[GI_NCON];
+      if (nefc) {
+        int rows = g[GI_NSIMPLE];
+        for (int ci = 0; ci < g[GI_NCON]; ci++) { int dim = g[GI_CON + 4 * ci + 2]; rows += dim == 1 ? 1 : 2 * (dim - 1); }
+        nefc[e] = rows;
+      }
+    }
+  }
+  return 0;
+}
+
+int adroit_reduce_episode(adroit_sim* s, int flush_running, double* out4_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  CK(cudaMemsetAsync(s->d_out4, 0, 4 * sizeof(double), st));
+  int thr = s->task == T_PEN ? 20 : 25;
+  int blocks = (s->n + 255) / 256;
+  if (blocks > 592) blocks = 592;
+  if (s->f64) reduce_kernel<<<blocks, 256, 0, st>>>(s->sd.acc, s->sd.t, s->sd.ep_goal, nullptr, s->sd.ep_return, s->n, thr, flush_running, s->d_out4);
+  else reduce_kernel<<<blocks, 256, 0, st>>>(s->sf.acc, s->sf.t, s->sf.ep_goal, s->sf.ep_return, nullptr, s->n, thr, flush_running, s->d_out4);
+  CK(cudaGetLastError());
+  s->launches++;
+  CK(cudaMemcpyAsync(out4_host, s->d_out4, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int64_t adroit_launch_count(const adroit_sim* s) { return s->launches; }
+
+int adroit_overflow(adroit_sim* s, int64_t* out2_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  unsigned long long v[2];
+  CK(cudaMemcpyAsync(v, s->f64 ? s->sd.overflow : s->sf.overflow, sizeof v, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  out2_host[0] = (int64_t)v[0];
+  out2_host[1] = (int64_t)v[1];
+  return 0;
+}
+
+// debug: raw per-env scratch block (fp64 host buffer [n][count]) starting at T-offset `offset`; layout in csrc/model.cuh
+int adroit_debug_scratch(adroit_sim* s, int offset, int count, double* out_host, void* stream) {
+  CK(cudaSetDevice(s->device));
+  return download_field(s, out_host, STF(scratch), count, G_TOTAL, offset, (cudaStream_t)stream);
+}
+int adroit_debug_iscratch(adroit_sim* s, int32_t* out_host, void* stream) {
+  CK(cudaSetDevice(s->device));
+  CK(cudaMemcpyAsync(out_host, s->f64 ? s->sd.iscratch : s->sf.iscratch, (size_t)s->n * GI_TOTAL * sizeof(int), cudaMemcpyDeviceToHost,
+                     (cudaStream_t)stream));
+  CK(cudaStreamSynchronize((cudaStream_t)stream));
+  return 0;
+}
+int adroit_debug_layout(int* out, int max_n) {
+  const int v[] = {NVP, NBP, NGP, NSP, MAXCON, CROWS, NTRI, NPARP, NTF, G_TOTAL, GI_TOTAL, G_GPOS, G_GMAT, G_SPOS, G_CON, G_JR, G_MINV,
+                   G_DBG_M, G_DBG_BIAS, G_DBG_QFS, G_DBG_QAS, G_DBG_QACC, G_DBG_QFC, G_DBG_XPOS, G_DBG_XQUAT, G_DBG_EF, GI_CON};
+  int n = (int)(sizeof v / sizeof v[0]);
+  for (int i = 0; i < n && i < max_n; i++) out[i] = v[i];
+  return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,733 @@
+// constraint.cuh — collision driver, constraint rows, Newton solver, noslip pass, touch sensor, Euler step.
+//
+// Restates MuJoCo 2.1's soft-constraint pipeline for the row types the Adroit scenes produce:
+// dof friction loss, joint limits, fixed-tendon limits and pyramidal contacts (condim 1/3/4), solved in primal
+// space by Newton's method with an exact line search, followed by the noslip Gauss-Seidel pass on friction rows.
+//
+// Representation (B200-first, not MuJoCo's dense efc_J):
+//   * "simple" rows (friction / limits) are never materialised: J is a signed unit vector (2 entries for a tendon);
+//   * a contact stores its 4-row contact-frame Jacobian Jf (normal, tangent1, tangent2, torsion) once; the 1/4/6
+//     pyramid edges are the combinations Jn +- mu_k Jt_k, evaluated on the fly from Jf*x (4 dot products per contact
+//     instead of 6 rows), and the Hessian contribution is Jf^T W Jf with a 4x4 weight W built from the edge states;
+//   * the noslip pass is matrix-free in acceleration space: with u = M^-1 J^T f the residual of a row is J_i u + b_i,
+//     so A = J M^-1 J^T (nefc^2 entries) is never formed.
+#pragma once
+#include "dynamics.cuh"
+
+namespace adroit {
+
+template <typename T> DI T impedance(const DModel<T>& m, T pos, T margin) {
+  T s0 = tclamp(m.solimp[0], T(0.0001), T(0.9999)), s1 = tclamp(m.solimp[1], T(0.0001), T(0.9999)), width = m.solimp[2];
+  T mid = tclamp(m.solimp[3], T(0.0001), T(0.9999)), power = m.solimp[4] < 1 ? T(1) : m.solimp[4];
+  if (s0 == s1 || width <= T(1e-15)) return T(0.5) * (s0 + s1);
+  T x = tabs((pos - margin) / width);
+  if (x >= 1) return s1;
+  if (x <= 0) return s0;
+  T y;
+  if (power == T(1)) y = x;
+  else if (power == T(2)) y = x <= mid ? x * x / mid : 1 - (1 - x) * (1 - x) / (1 - mid);
+  else if (x <= mid) y = pow(x, power) / pow(mid, power - 1);
+  else y = 1 - pow(1 - x, power) / pow(1 - mid, power - 1);
+  return s0 + y * (s1 - s0);
+}
+template <typename T> DI void sol_KB(const DModel<T>& m, T& K, T& B) {
+  T tc = tmax(m.solref[0], 2 * m.timestep), dmax = tclamp(m.solimp[1], T(0.0001), T(0.9999));
+  K = T(1) / tmax(T(1e-15), dmax * dmax * tc * tc * m.solref[1] * m.solref[1]);
+  B = T(2) / tmax(T(1e-15), dmax * tc);
+}
+
+// ---------------------------------------------------------------- collision over the static candidate list
+template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned long long* overflow) {
+  const DModel<T>& m = c.m;
+  const T *gpos = c.g + G_GPOS, *gmat = c.g + G_GMAT;
+  int* surv = c.si + I_SURV;
+  const unsigned lt = (1u << c.lane) - 1u;
+  int nsurv = 0;
+  for (int base = 0; base < m.npair; base += 32) {
+    int k = base + c.lane;
+    bool hit = false;
+    if (k < m.npair) {
+      int g1 = m.pair_geom[2 * k], g2 = m.pair_geom[2 * k + 1];
+      T margin = m.pair_margin[k];
+      T dx = gpos[3 * g2] - gpos[3 * g1], dy = gpos[3 * g2 + 1] - gpos[3 * g1 + 1], dz = gpos[3 * g2 + 2] - gpos[3 * g1 + 2];
+      if (m.geom_type[g1] == G_PLANE) {
+        const T* R = gmat + 9 * g1;
+        hit = !(dx * R[2] + dy * R[5] + dz * R[8] > m.geom_rbound[g2] + margin);
+      } else {
+        T bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
+        hit = !(dx * dx + dy * dy + dz * dz > bound * bound);
+      }
+    }
+    unsigned mask = __ballot_sync(0xffffffffu, hit);
+    if (hit) {
+      int p = nsurv + __popc(mask & lt);
+      if (p < MAXSURV) surv[p] = k;
+    }
+    nsurv += __popc(mask);
+  }
+  if (nsurv > MAXSURV) {
+    if (c.lane == 0) atomicAdd(overflow, (unsigned long long)(nsurv - MAXSURV));
+    nsurv = MAXSURV;
+  }
+  __syncwarp();
+  int ncon = 0;
+  T* cmu = c.s + O_CMU;
+  for (int base = 0; base < nsurv; base += 32) {
+    ConOut<T> out;
+    out.n = 0;
+    int i = base + c.lane, k = -1, g1 = 0, g2 = 0;
+    V3<T> origin = mk<T>(0, 0, 0);
+    if (i < nsurv) {
+      k = surv[i];
+      g1 = m.pair_geom[2 * k];
+      g2 = m.pair_geom[2 * k + 1];
+      M3<T> R1, R2;
+      for (int e = 0; e < 9; e++) { R1.m[e] = gmat[9 * g1 + e]; R2.m[e] = gmat[9 * g2 + e]; }
+      origin = mk<T>(gpos[3 * g1], gpos[3 * g1 + 1], gpos[3 * g1 + 2]);
+      V3<T> p2 = mk<T>(gpos[3 * g2], gpos[3 * g2 + 1], gpos[3 * g2 + 2]) - origin;
+      V3<T> s1 = mk<T>(m.geom_size[3 * g1], m.geom_size[3 * g1 + 1], m.geom_size[3 * g1 + 2]);
+      V3<T> s2 = mk<T>(m.geom_size[3 * g2], m.geom_size[3 * g2 + 1], m.geom_size[3 * g2 + 2]);
+      collide_pair(out, m.pair_margin[k], m.geom_type[g1], mk<T>(0, 0, 0), R1, s1, m.geom_type[g2], p2, R2, s2,
+                   m.mpr_iterations, m.mpr_tolerance);
+    }
+    // ordered compaction: contacts keep candidate-list order (the noslip sweep order depends on it)
+    int cnt = out.n, incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (c.lane >= o) incl += t;
+    }
+    int total = __shfl_sync(0xffffffffu, incl, 31), excl = incl - cnt;
+    for (int q = 0; q < cnt; q++) {
+      int ci = ncon + excl + q;
+      if (ci >= MAXCON) break;
+      T* C = c.g + G_CON + 16 * ci;
+      V3<T> pos = out.pos[q] + origin, x = normalized(out.nrm[q]);
+      V3<T> y = (x.y > T(0.5) || x.y < T(-0.5)) ? mk<T>(0, 0, 1) : mk<T>(0, 1, 0);
+      y = normalized(y - x * dot(x, y));
+      V3<T> z = cross(x, y);
+      C[0] = out.dist[q];
+      C[1] = pos.x; C[2] = pos.y; C[3] = pos.z;
+      C[4] = x.x; C[5] = x.y; C[6] = x.z; C[7] = y.x; C[8] = y.y; C[9] = y.z; C[10] = z.x; C[11] = z.y; C[12] = z.z;
+      C[13] = m.pair_margin[k];
+      c.si[I_CDIM + ci] = m.pair_condim[k];
+      c.si[I_CB1 + ci] = m.geom_body[g1];
+      c.si[I_CB2 + ci] = m.geom_body[g2];
+      cmu[3 * ci] = m.pair_friction[5 * k];
+      cmu[3 * ci + 1] = m.pair_friction[5 * k + 1];
+      cmu[3 * ci + 2] = m.pair_friction[5 * k + 2];
+      c.gi[GI_CON + 4 * ci] = g1;
+      c.gi[GI_CON + 4 * ci + 1] = g2;
+      c.gi[GI_CON + 4 * ci + 2] = m.pair_condim[k];
+    }
+    ncon += total;
+  }
+  if (ncon > MAXCON) {
+    if (c.lane == 0) atomicAdd(overflow, (unsigned long long)(ncon - MAXCON));
+    ncon = MAXCON;
+  }
+  c.ncon = ncon;
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------- constraint rows
+template <typename T> DI int n_edges(int dim) { return dim == 1 ? 1 : 2 * (dim - 1); }
+
+template <typename T> __device__ __noinline__ void make_constraint(Ctx<T>& c, unsigned long long* overflow) {
+  const DModel<T>& m = c.m;
+  const T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL);
+  int* sinfo = c.si + I_SINFO;
+  T *sD = c.s + O_SD, *saref = c.s + O_SAREF, *sfl = c.s + O_SFL, *sforce = c.s + O_SFORCE;
+  const unsigned lt = (1u << c.lane) - 1u;
+  T K, B;
+  sol_KB(m, K, B);
+  int nrow = 0, dropped = 0;
+  // friction loss (one row per dof with frictionloss > 0)
+  for (int base = 0; base < m.nv; base += 32) {
+    int j = base + c.lane;
+    bool has = j < m.nv && m.dof_frictionloss[j] > 0;
+    unsigned mask = __ballot_sync(0xffffffffu, has);
+    int r = nrow + __popc(mask & lt);
+    if (has && r < MAXSIMPLE) {
+      T imp = impedance(m, T(0), T(0));
+      T R = tmax(T(1e-15), (1 - imp) * m.dof_invweight0[j] / imp);
+      sinfo[r] = S_FRICTION | (j << 2);
+      sD[r] = T(1) / R;
+      saref[r] = -B * qvel[j];
+      sfl[r] = m.dof_frictionloss[j];
+      sforce[r] = 0;
+    }
+    nrow += __popc(mask);
+  }
+  // joint limits: q = 2*j + (upper side)
+  for (int base = 0; base < 2 * m.nv; base += 32) {
+    int q = base + c.lane, j = q >> 1, up = q & 1;
+    bool has = false;
+    T dist = 0;
+    if (j < m.nv && m.jnt_limited[j]) {
+      dist = up ? m.jnt_range[2 * j + 1] - qpos[j] : qpos[j] - m.jnt_range[2 * j];
+      has = dist < m.jnt_margin[j];
+    }
+    unsigned mask = __ballot_sync(0xffffffffu, has);
+    int r = nrow + __popc(mask & lt);
+    if (has && r < MAXSIMPLE) {
+      T mg = m.jnt_margin[j], imp = impedance(m, dist, mg);
+      T R = tmax(T(1e-15), (1 - imp) * m.dof_invweight0[j] / imp);
+      T vel = up ? -qvel[j] : qvel[j];
+      sinfo[r] = S_JLIMIT | (j << 2) | (up << 12);
+      sD[r] = T(1) / R;
+      saref[r] = -B * vel - K * imp * (dist - mg);
+      sfl[r] = 0;
+      sforce[r] = 0;
+    }
+    nrow += __popc(mask);
+  }
+  // tendon limits
+  for (int base = 0; base < 2 * m.ntendon; base += 32) {
+    int q = base + c.lane, t = q >> 1, up = q & 1;
+    bool has = false;
+    T dist = 0, vel = 0;
+    if (t < m.ntendon && m.tendon_limited[t]) {
+      T len = 0;
+      for (int k = 0; k < 2; k++) {
+        int dj = m.tendon_dof[2 * t + k];
+        if (dj >= 0) { len += m.tendon_coef[2 * t + k] * qpos[dj]; vel += m.tendon_coef[2 * t + k] * qvel[dj]; }
+      }
+      dist = up ? m.tendon_range[2 * t + 1] - len : len - m.tendon_range[2 * t];
+      has = dist < m.tendon_margin[t];
+    }
+    unsigned mask = __ballot_sync(0xffffffffu, has);
+    int r = nrow + __popc(mask & lt);
+    if (has && r < MAXSIMPLE) {
+      T mg = m.tendon_margin[t], imp = impedance(m, dist, mg);
+      T R = tmax(T(1e-15), (1 - imp) * m.tendon_invweight0[t] / imp);
+      sinfo[r] = S_TLIMIT | (t << 2) | (up << 12);
+      sD[r] = T(1) / R;
+      saref[r] = -B * (up ? -vel : vel) - K * imp * (dist - mg);
+      sfl[r] = 0;
+      sforce[r] = 0;
+    }
+    nrow += __popc(mask);
+  }
+  if (nrow > MAXSIMPLE) { dropped = nrow - MAXSIMPLE; nrow = MAXSIMPLE; }
+  if (dropped && c.lane == 0) atomicAdd(overflow + 1, (unsigned long long)dropped);
+  c.nsimple = nrow;
+
+  // contacts: contact-frame Jacobian rows (both layouts), frame velocity, impedance
+  const T *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS;
+  T *JR = c.g + G_JR, *JT = c.g + G_JT;
+  T *cD = c.s + O_CD, *cmu = c.s + O_CMU, *carefn = c.s + O_CAREFN, *cbt = c.s + O_CBT, *ef = c.s + O_EF;
+  for (int ci = 0; ci < c.ncon; ci++) {
+    const T* C = c.g + G_CON + 16 * ci;
+    int b1 = c.si[I_CB1 + ci], b2 = c.si[I_CB2 + ci], dim = c.si[I_CDIM + ci];
+    unsigned long long m1 = m.body_dofmask[b1], m2 = m.body_dofmask[b2];
+    T vsum[4] = {0, 0, 0, 0};
+    for (int j = c.lane; j < NVP; j += 32) {
+      T row[4] = {0, 0, 0, 0};
+      if (j < m.nv) {
+        int sg = (int)((m2 >> j) & 1ull) - (int)((m1 >> j) & 1ull);
+        if (sg != 0) {
+          const T* a = xaxis + 3 * j;
+          T jp[3], jr[3] = {0, 0, 0};
+          if (m.jnt_type[j] == J_SLIDE) { jp[0] = a[0]; jp[1] = a[1]; jp[2] = a[2]; }
+          else {
+            T r[3] = {C[1] - xanc[3 * j], C[2] - xanc[3 * j + 1], C[3] - xanc[3 * j + 2]};
+            cross3(jp, a, r);
+            jr[0] = a[0]; jr[1] = a[1]; jr[2] = a[2];
+          }
+          T s = (T)sg;
+          row[0] = s * (C[4] * jp[0] + C[5] * jp[1] + C[6] * jp[2]);
+          row[1] = s * (C[7] * jp[0] + C[8] * jp[1] + C[9] * jp[2]);
+          row[2] = s * (C[10] * jp[0] + C[11] * jp[1] + C[12] * jp[2]);
+          row[3] = s * (C[4] * jr[0] + C[5] * jr[1] + C[6] * jr[2]);
+          for (int a4 = 0; a4 < 4; a4++) vsum[a4] += row[a4] * qvel[j];
+        }
+      }
+      for (int a4 = 0; a4 < 4; a4++) {
+        JR[(4 * ci + a4) * NVP + j] = row[a4];
+        JT[j * CROWS + 4 * ci + a4] = row[a4];
+      }
+    }
+    for (int a4 = 0; a4 < 4; a4++) vsum[a4] = warp_sum(vsum[a4]);
+    if (c.lane == 0) {
+      T dist = C[0], mg = C[13], imp = impedance(m, dist, mg);
+      T tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
+      T mu0 = cmu[3 * ci];
+      T diag = dim == 1 ? tran : tran + mu0 * mu0 * tran;
+      T R = tmax(T(1e-15), (1 - imp) * diag / imp);
+      if (dim > 1) { T mu = mu0 * sqrt(T(1) / m.impratio); R = 2 * mu * mu * R; }
+      cD[ci] = T(1) / R;
+      carefn[ci] = -B * vsum[0] - K * imp * (dist - mg);
+      for (int k = 0; k < 3; k++) cbt[3 * ci + k] = (k + 2 <= dim) ? -B * cmu[3 * ci + k] * vsum[k + 1] : T(0);
+      for (int e = 0; e < 6; e++) ef[6 * ci + e] = 0;
+    }
+  }
+  __syncwarp();
+}
+
+// J_r . x for a simple row
+template <typename T> DI T simple_dot(const DModel<T>& m, int info, const T* x) {
+  int kind = info & 3, id = (info >> 2) & 1023, up = (info >> 12) & 1;
+  if (kind == S_FRICTION) return x[id];
+  if (kind == S_JLIMIT) return up ? -x[id] : x[id];
+  T s = 0;
+  for (int k = 0; k < 2; k++) {
+    int dj = m.tendon_dof[2 * id + k];
+    if (dj >= 0) s += m.tendon_coef[2 * id + k] * x[dj];
+  }
+  return up ? -s : s;
+}
+// contact-frame products  out[ci][a] = Jf[ci][a] . x   (lanes over rows, dof-major layout -> coalesced)
+template <typename T> DI void contact_frame_mul(Ctx<T>& c, const T* x, T* out) {
+  const T* JT = c.g + G_JT;
+  int nrows = 4 * c.ncon;
+  for (int r = c.lane; r < nrows; r += 32) {
+    T s = 0;
+    for (int j = 0; j < c.m.nv; j++) s += JT[j * CROWS + r] * x[j];
+    out[r] = s;
+  }
+}
+// edge e of contact ci: value of (Jn + sign*mu_k*Jt_k).x given the frame product fx[4]
+template <typename T> DI T edge_val(const T* fx, const T* mu, int dim, int e, T& sign, int& k) {
+  if (dim == 1) { sign = 0; k = 0; return fx[0]; }
+  k = e >> 1;
+  sign = (e & 1) ? T(-1) : T(1);
+  return fx[0] + sign * mu[k] * fx[k + 1];
+}
+
+// cost, forces and states at the point whose frame accelerations are in O_AC and dof accelerations in `qacc`.
+// Returns the constraint cost (all lanes).  Also accumulates J^T f into V_QFC when `want_qfc`.
+template <typename T> __device__ __noinline__ T constraint_update(Ctx<T>& c, const T* qacc, bool want_qfc) {
+  const DModel<T>& m = c.m;
+  int* sinfo = c.si + I_SINFO;
+  const T *sD = c.s + O_SD, *saref = c.s + O_SAREF, *sfl = c.s + O_SFL;
+  T *sforce = c.s + O_SFORCE, *qfc = c.v(V_QFC);
+  T cost = 0;
+  if (want_qfc) {
+    for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
+    __syncwarp();
+  }
+  for (int r = c.lane; r < c.nsimple; r += 32) {
+    int info = sinfo[r] & 0x1fff;
+    T jar = simple_dot(m, info, qacc) - saref[r], D = sD[r], f;
+    int state;
+    if ((info & 3) == S_FRICTION) {
+      T fl = sfl[r], rf = fl / D;
+      if (jar <= -rf) { f = fl; state = 0; cost += -T(0.5) * rf * fl - fl * jar; }
+      else if (jar >= rf) { f = -fl; state = 0; cost += -T(0.5) * rf * fl + fl * jar; }
+      else { f = -D * jar; state = 1; cost += T(0.5) * D * jar * jar; }
+    } else if (jar < 0) { f = -D * jar; state = 1; cost += T(0.5) * D * jar * jar; }
+    else { f = 0; state = 0; }
+    sforce[r] = f;
+    sinfo[r] = info | (state << 13);
+    if (want_qfc && f != 0) {
+      int kind = info & 3, id = (info >> 2) & 1023, up = (info >> 12) & 1;
+      if (kind == S_FRICTION) atomicAdd(qfc + id, f);
+      else if (kind == S_JLIMIT) atomicAdd(qfc + id, up ? -f : f);
+      else
+        for (int k = 0; k < 2; k++) {
+          int dj = m.tendon_dof[2 * id + k];
+          if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tendon_coef[2 * id + k]);
+        }
+    }
+  }
+  // contacts: one lane per contact walks its edges; builds the 4x4 Hessian weight W and the frame force
+  const T *ac = c.s + O_AC, *cD = c.s + O_CD, *cmu = c.s + O_CMU, *carefn = c.s + O_CAREFN, *cbt = c.s + O_CBT;
+  T *ef = c.s + O_EF, *W = c.s + O_W;
+  for (int ci = c.lane; ci < c.ncon; ci += 32) {
+    int dim = c.si[I_CDIM + ci], ne = n_edges<T>(dim);
+    T D = cD[ci], w[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int e = 0; e < ne; e++) {
+      T sign;
+      int k;
+      T val = edge_val(ac + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
+      T jar = val - (carefn[ci] + sign * cbt[3 * ci + k]);
+      T f = 0;
+      if (jar < 0) {
+        f = -D * jar;
+        cost += T(0.5) * D * jar * jar;
+        T smu = sign * cmu[3 * ci + k];
+        w[0] += D;                       // W_nn
+        if (dim > 1) { w[1 + k] += D * smu; w[4 + k] += D * smu * smu; }  // W_nk, W_kk
+      }
+      ef[6 * ci + e] = f;
+    }
+    for (int q = 0; q < 7; q++) W[7 * ci + q] = w[q];
+  }
+  __syncwarp();
+  if (want_qfc && c.ncon > 0) {
+    // frame forces F[ci][4] into O_AV (scratch use), then qfc[j] += sum_r Jr[r][j] F[r]
+    T* F = c.s + O_AV;
+    for (int ci = c.lane; ci < c.ncon; ci += 32) {
+      int dim = c.si[I_CDIM + ci];
+      const T* f = ef + 6 * ci;
+      if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
+      else {
+        T fn = 0;
+        for (int e = 0; e < 2 * (dim - 1); e++) fn += f[e];
+        F[4 * ci] = fn;
+        for (int k = 0; k < 3; k++) F[4 * ci + 1 + k] = (k + 2 <= dim) ? cmu[3 * ci + k] * (f[2 * k] - f[2 * k + 1]) : T(0);
+      }
+    }
+    __syncwarp();
+    const T* JR = c.g + G_JR;
+    for (int j = c.lane; j < m.nv; j += 32) {
+      T s = 0;
+      for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
+      qfc[j] += s;
+    }
+    __syncwarp();
+  }
+  return warp_sum(cost);
+}
+
+// derivative pair (f', f'') of the constraint cost along qacc + alpha*search
+template <typename T> DI void ls_eval(Ctx<T>& c, T alpha, const T* qacc, const T* search, T& d1, T& d2) {
+  const DModel<T>& m = c.m;
+  const int* sinfo = c.si + I_SINFO;
+  const T *sD = c.s + O_SD, *saref = c.s + O_SAREF, *sfl = c.s + O_SFL;
+  T a = 0, b = 0;
+  for (int r = c.lane; r < c.nsimple; r += 32) {
+    int info = sinfo[r] & 0x1fff;
+    T x = simple_dot(m, info, qacc) - saref[r], y = simple_dot(m, info, search), D = sD[r], z = x + alpha * y;
+    if ((info & 3) == S_FRICTION) {
+      T fl = sfl[r], rf = fl / D;
+      if (z <= -rf) a += -fl * y;
+      else if (z >= rf) a += fl * y;
+      else { a += D * z * y; b += D * y * y; }
+    } else if (z < 0) { a += D * z * y; b += D * y * y; }
+  }
+  const T *ac = c.s + O_AC, *av = c.s + O_AV, *cD = c.s + O_CD, *cmu = c.s + O_CMU, *carefn = c.s + O_CAREFN, *cbt = c.s + O_CBT;
+  for (int t = c.lane; t < 6 * c.ncon; t += 32) {
+    int ci = t / 6, e = t - 6 * ci, dim = c.si[I_CDIM + ci];
+    if (e >= n_edges<T>(dim)) continue;
+    T sign;
+    int k;
+    T x = edge_val(ac + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
+    x -= carefn[ci] + sign * cbt[3 * ci + k];
+    T y = edge_val(av + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
+    T D = cD[ci], z = x + alpha * y;
+    if (z < 0) { a += D * z * y; b += D * y * y; }
+  }
+  d1 = warp_sum(a);
+  d2 = warp_sum(b);
+}
+
+// H (packed, O_H) = M + J^T D_active J, using the states / weights left by constraint_update
+template <typename T> __device__ __noinline__ void build_hessian(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  T *H = c.s + O_H, *M = c.s + O_M;
+  int ntri = (m.nv * (m.nv + 1)) / 2;
+  for (int p = c.lane; p < ntri; p += 32) H[p] = M[p];
+  __syncwarp();
+  const int* sinfo = c.si + I_SINFO;
+  const T* sD = c.s + O_SD;
+  for (int r = c.lane; r < c.nsimple; r += 32) {
+    int info = sinfo[r];
+    if (!((info >> 13) & 1)) continue;
+    int kind = info & 3, id = (info >> 2) & 1023;
+    T D = sD[r];
+    if (kind != S_TLIMIT) atomicAdd(H + tri(id, id), D);
+    else {
+      int d0 = m.tendon_dof[2 * id], d1 = m.tendon_dof[2 * id + 1];
+      T c0 = m.tendon_coef[2 * id], c1 = m.tendon_coef[2 * id + 1];
+      if (d0 >= 0) atomicAdd(H + tri(d0, d0), D * c0 * c0);
+      if (d1 >= 0) atomicAdd(H + tri(d1, d1), D * c1 * c1);
+      if (d0 >= 0 && d1 >= 0) atomicAdd(H + (d0 > d1 ? tri(d0, d1) : tri(d1, d0)), D * c0 * c1);
+    }
+  }
+  __syncwarp();
+  const T *JR = c.g + G_JR, *W = c.s + O_W;
+  for (int ci = 0; ci < c.ncon; ci++) {
+    const T* w = W + 7 * ci;
+    if (w[0] == 0) continue;  // no active edge (warp-uniform: shared memory value)
+    T v0[4], v1[4], g0[4], g1[4];
+    int j0 = c.lane, j1 = c.lane + 32;
+    bool nz0 = false, nz1 = false;
+    for (int a = 0; a < 4; a++) {
+      v0[a] = JR[(4 * ci + a) * NVP + j0];
+      v1[a] = j1 < NVP ? JR[(4 * ci + a) * NVP + j1] : T(0);
+      nz0 |= v0[a] != 0;
+      nz1 |= v1[a] != 0;
+    }
+    g0[0] = w[0] * v0[0] + w[1] * v0[1] + w[2] * v0[2] + w[3] * v0[3];
+    g1[0] = w[0] * v1[0] + w[1] * v1[1] + w[2] * v1[2] + w[3] * v1[3];
+    for (int k = 0; k < 3; k++) {
+      g0[1 + k] = w[1 + k] * v0[0] + w[4 + k] * v0[1 + k];
+      g1[1 + k] = w[1 + k] * v1[0] + w[4 + k] * v1[1 + k];
+    }
+    unsigned mk0 = __ballot_sync(0xffffffffu, nz0), mk1 = __ballot_sync(0xffffffffu, nz1);
+    while (mk0) {
+      int i = __ffs(mk0) - 1;
+      mk0 &= mk0 - 1;
+      T s = 0;
+      for (int a = 0; a < 4; a++) s += __shfl_sync(0xffffffffu, v0[a], i) * g0[a];
+      if (j0 <= i && nz0) H[tri(i, j0)] += s;
+    }
+    while (mk1) {
+      int i = __ffs(mk1) - 1;
+      mk1 &= mk1 - 1;
+      T s0 = 0, s1 = 0;
+      for (int a = 0; a < 4; a++) {
+        T vi = __shfl_sync(0xffffffffu, v1[a], i);
+        s0 += vi * g0[a];
+        s1 += vi * g1[a];
+      }
+      int ii = i + 32;
+      if (nz0) H[tri(ii, j0)] += s0;
+      if (j1 <= ii && nz1) H[tri(ii, j1)] += s1;
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------- Newton solver (primal, exact line search)
+template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  const int nv = m.nv, lane = c.lane;
+  T *qacc = c.v(V_QACC), *Ma = c.v(V_MA), *grad = c.v(V_GRAD), *search = c.v(V_SEARCH), *Mv = c.v(V_MV), *qfc = c.v(V_QFC);
+  const T *qfs = c.v(V_QFS), *qas = c.v(V_QAS), *warm = c.v(V_WARM);
+  T *M = c.s + O_M, *H = c.s + O_H, *ac = c.s + O_AC, *av = c.s + O_AV;
+  const T scale = T(1) / (m.meaninertia * (nv > 1 ? nv : 1));
+
+  // cost at the warm start and at qacc_smooth (Gauss term vanishes there)
+  auto gauss = [&](const T* a, const T* Maa) {
+    T s = 0;
+    for (int j = lane; j < nv; j += 32) s += T(0.5) * (Maa[j] - qfs[j]) * (a[j] - qas[j]);
+    return warp_sum(s);
+  };
+  symv_packed(M, warm, Ma, nv, lane);
+  contact_frame_mul(c, warm, ac);
+  __syncwarp();
+  T cost_ws = constraint_update(c, warm, false) + gauss(warm, Ma);
+  contact_frame_mul(c, qas, ac);
+  __syncwarp();
+  T cost_sm = constraint_update(c, qas, false);
+  bool use_ws = cost_ws < cost_sm;
+  for (int j = lane; j < nv; j += 32) qacc[j] = use_ws ? warm[j] : qas[j];
+  __syncwarp();
+  symv_packed(M, qacc, Ma, nv, lane);
+  contact_frame_mul(c, qacc, ac);
+  __syncwarp();
+  T cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
+  int iters = 0;
+  for (int iter = 0; iter < m.iterations; iter++) {
+    T g2 = 0;
+    for (int j = lane; j < nv; j += 32) {
+      T g = Ma[j] - qfs[j] - qfc[j];
+      grad[j] = g;
+      search[j] = -g;
+      g2 += g * g;
+    }
+    g2 = warp_sum(g2);
+    if (scale * sqrt(g2) < m.tolerance) break;
+    build_hessian(c);
+    chol_packed(H, nv, lane);
+    chol_solve_packed(H, search, nv, lane);
+    symv_packed(M, search, Mv, nv, lane);
+    contact_frame_mul(c, search, av);
+    __syncwarp();
+    // exact line search on the convex piecewise-quadratic: safeguarded Newton on f'(alpha)
+    T A0 = 0, B0 = 0;
+    for (int j = lane; j < nv; j += 32) { A0 += search[j] * Mv[j]; B0 += search[j] * (Ma[j] - qfs[j]); }
+    A0 = warp_sum(A0);
+    B0 = warp_sum(B0);
+    T d1, d2;
+    ls_eval(c, T(0), qacc, search, d1, d2);
+    T f1 = B0 + d1, f2 = A0 + d2;
+    T alpha = 0;
+    if (f1 < 0) {
+      const T gtol = (sizeof(T) == 4 ? T(1e-6) : T(1e-13)) * (-f1);
+      T lo = 0, hi = -1;  // hi < 0: unbounded
+      alpha = -f1 / f2;
+      for (int it = 0; it < 40; it++) {
+        ls_eval(c, alpha, qacc, search, d1, d2);
+        T fa = A0 * alpha + B0 + d1, fb = A0 + d2;
+        if (tabs(fa) <= gtol) break;
+        if (fa < 0) lo = alpha; else hi = alpha;
+        T nxt = alpha - fa / fb;
+        bool inside = nxt > lo && (hi < 0 || nxt < hi);
+        if (!inside) nxt = hi < 0 ? 2 * alpha : T(0.5) * (lo + hi);
+        if (hi >= 0 && (hi - lo) <= (sizeof(T) == 4 ? T(1e-7) : T(1e-15)) * hi) { alpha = nxt; break; }
+        alpha = nxt;
+      }
+    }
+    if (alpha == 0) break;
+    for (int j = lane; j < nv; j += 32) { qacc[j] += alpha * search[j]; Ma[j] += alpha * Mv[j]; }
+    for (int r = lane; r < 4 * c.ncon; r += 32) ac[r] += alpha * av[r];
+    __syncwarp();
+    T old = cost;
+    cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
+    iters = iter + 1;
+    if (scale * (old - cost) < m.tolerance) break;
+  }
+  if (lane == 0) c.gi[GI_NITER] = iters;
+}
+
+// ---------------------------------------------------------------- noslip (Gauss-Seidel on friction rows, matrix-free)
+template <typename T> __device__ __noinline__ void noslip(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  const int nv = m.nv, lane = c.lane;
+  const T *Minv = c.g + G_MINV, *JR = c.g + G_JR, *qas = c.v(V_QAS);
+  T *u = c.v(V_GRAD), *tmp = c.v(V_SEARCH), *qfc = c.v(V_QFC), *YT = c.g + G_YT;
+  const int* sinfo = c.si + I_SINFO;
+  const T *saref = c.s + O_SAREF, *sfl = c.s + O_SFL, *cmu = c.s + O_CMU, *cbt = c.s + O_CBT;
+  T *sforce = c.s + O_SFORCE, *ef = c.s + O_EF;
+  // u = M^-1 J^T f  (qfc holds J^T f from the last constraint_update)
+  symv_packed(Minv, qfc, u, nv, lane);
+  // Yt[ci][k] = M^-1 Jt_k^T and K1 = 4 mu_k^2 Jt_k.Yt_k (kept in O_AV[ci*4+1+k])
+  T* K1 = c.s + O_AV;
+  for (int ci = 0; ci < c.ncon; ci++) {
+    int dim = c.si[I_CDIM + ci];
+    for (int k = 0; k + 2 <= dim && k < 3; k++) {
+      const T* Jt = JR + (4 * ci + 1 + k) * NVP;
+      for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
+      __syncwarp();
+      T dsum = 0;
+      for (int i = lane; i < nv; i += 32) {
+        T s = 0;
+        for (int j = 0; j < nv; j++) s += sym_get(Minv, i, j) * tmp[j];
+        YT[(3 * ci + k) * NVP + i] = s;
+        dsum += s * tmp[i];
+      }
+      dsum = warp_sum(dsum);
+      if (lane == 0) K1[4 * ci + 1 + k] = 4 * cmu[3 * ci + k] * cmu[3 * ci + k] * dsum;
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  const T scale = T(1) / (m.meaninertia * (nv > 1 ? nv : 1));
+  int sweeps = 0;
+  for (int iter = 0; iter < m.noslip_iterations; iter++) {
+    T improvement = 0;
+    for (int r = 0; r < c.nsimple; r++) {
+      int info = sinfo[r];
+      if ((info & 3) != S_FRICTION) break;  // friction rows come first
+      int dj = (info >> 2) & 1023;
+      T res = u[dj] + qas[dj] - saref[r], Aii = Minv[tri(dj, dj)], old = sforce[r], fl = sfl[r];
+      T f = tclamp(old - res / Aii, -fl, fl), delta = f - old;
+      __syncwarp();
+      if (delta != 0) {
+        for (int j = lane; j < nv; j += 32) u[j] += delta * sym_get(Minv, j, dj);
+        if (lane == 0) sforce[r] = f;
+        improvement -= T(0.5) * delta * delta * Aii + delta * res;
+      }
+      __syncwarp();
+    }
+    for (int ci = 0; ci < c.ncon; ci++) {
+      int dim = c.si[I_CDIM + ci];
+      for (int k = 0; k + 2 <= dim && k < 3; k++) {
+        const T* Jt = JR + (4 * ci + 1 + k) * NVP;
+        T s = 0;
+        for (int j = lane; j < nv; j += 32) s += Jt[j] * (u[j] + qas[j]);
+        s = warp_sum(s);
+        T mu = cmu[3 * ci + k], g = 2 * mu * s - 2 * cbt[3 * ci + k], k1 = K1[4 * ci + 1 + k];
+        T f0 = ef[6 * ci + 2 * k], f1 = ef[6 * ci + 2 * k + 1], mid = T(0.5) * (f0 + f1), yold = T(0.5) * (f0 - f1), y = yold;
+        if (k1 >= T(1e-15)) y = tclamp(yold - g / k1, -mid, mid);
+        else y = 0;
+        T dy = y - yold;
+        __syncwarp();
+        if (dy != 0) {
+          const T* Y = YT + (3 * ci + k) * NVP;
+          for (int j = lane; j < nv; j += 32) u[j] += 2 * mu * dy * Y[j];
+          if (lane == 0) { ef[6 * ci + 2 * k] = mid + y; ef[6 * ci + 2 * k + 1] = mid - y; }
+          improvement -= T(0.5) * k1 * dy * dy + g * dy;
+        }
+        __syncwarp();
+      }
+    }
+    sweeps = iter + 1;
+    if (scale * improvement < m.noslip_tolerance) break;
+  }
+  if (lane == 0) c.gi[GI_NSLIP] = sweeps;
+  __syncwarp();
+}
+
+// qfrc_constraint = J^T f from the stored forces (V_QFC)
+template <typename T> __device__ __noinline__ void constraint_force(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  T *qfc = c.v(V_QFC), *F = c.s + O_AV;
+  const int* sinfo = c.si + I_SINFO;
+  const T *sforce = c.s + O_SFORCE, *ef = c.s + O_EF, *cmu = c.s + O_CMU;
+  for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
+  __syncwarp();
+  for (int r = c.lane; r < c.nsimple; r += 32) {
+    T f = sforce[r];
+    if (f == 0) continue;
+    int info = sinfo[r], kind = info & 3, id = (info >> 2) & 1023, up = (info >> 12) & 1;
+    if (kind == S_FRICTION) atomicAdd(qfc + id, f);
+    else if (kind == S_JLIMIT) atomicAdd(qfc + id, up ? -f : f);
+    else
+      for (int k = 0; k < 2; k++) {
+        int dj = m.tendon_dof[2 * id + k];
+        if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tendon_coef[2 * id + k]);
+      }
+  }
+  for (int ci = c.lane; ci < c.ncon; ci += 32) {
+    int dim = c.si[I_CDIM + ci];
+    const T* f = ef + 6 * ci;
+    if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
+    else {
+      T fn = 0;
+      for (int e = 0; e < 2 * (dim - 1); e++) fn += f[e];
+      F[4 * ci] = fn;
+      for (int k = 0; k < 3; k++) F[4 * ci + 1 + k] = (k + 2 <= dim) ? cmu[3 * ci + k] * (f[2 * k] - f[2 * k + 1]) : T(0);
+    }
+  }
+  __syncwarp();
+  const T* JR = c.g + G_JR;
+  for (int j = c.lane; j < m.nv; j += 32) {
+    T s = 0;
+    for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
+    qfc[j] += s;
+  }
+  __syncwarp();
+}
+
+// touch sensor S_nail (hammer_v0.py:102): normal forces of contacts on the site's body whose contact ray hits the site cylinder
+template <typename T> DI bool ray_hits_cylinder(const T* spos, const T* smat, const T* size, const T* pnt, const T* vec) {
+  T t[3] = {pnt[0] - spos[0], pnt[1] - spos[1], pnt[2] - spos[2]}, o[3], v[3];
+  for (int i = 0; i < 3; i++) {
+    o[i] = smat[i] * t[0] + smat[3 + i] * t[1] + smat[6 + i] * t[2];
+    v[i] = smat[i] * vec[0] + smat[3 + i] * vec[1] + smat[6 + i] * vec[2];
+  }
+  T r = size[0], h = size[1];
+  if (o[0] * o[0] + o[1] * o[1] <= r * r && tabs(o[2]) <= h) return true;
+  T a = v[0] * v[0] + v[1] * v[1], b = o[0] * v[0] + o[1] * v[1], cc = o[0] * o[0] + o[1] * o[1] - r * r;
+  if (a > tiny<T>()) {
+    T det = b * b - a * cc;
+    if (det >= 0) {
+      T sq = sqrt(det);
+      for (int k = -1; k <= 1; k += 2) {
+        T x = (-b + k * sq) / a;
+        if (x >= 0 && tabs(o[2] + x * v[2]) <= h) return true;
+      }
+    }
+  }
+  if (tabs(v[2]) > tiny<T>())
+    for (int k = -1; k <= 1; k += 2) {
+      T x = (k * h - o[2]) / v[2], px = o[0] + x * v[0], py = o[1] + x * v[1];
+      if (x >= 0 && px * px + py * py <= r * r) return true;
+    }
+  return false;
+}
+template <typename T> __device__ __noinline__ T touch_sensor(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  if (m.touch_site < 0) return T(0);
+  int sb = m.site_body[m.touch_site];
+  const T *ef = c.s + O_EF, *spos = c.g + G_SPOS + 3 * m.touch_site, *smat = c.s + O_XMAT + 9 * sb;
+  T sum = 0;
+  for (int ci = c.lane; ci < c.ncon; ci += 32) {
+    int b1 = c.si[I_CB1 + ci], b2 = c.si[I_CB2 + ci], dim = c.si[I_CDIM + ci];
+    if (sb != b1 && sb != b2) continue;
+    T fn = 0;
+    for (int e = 0; e < n_edges<T>(dim); e++) fn += ef[6 * ci + e];
+    if (fn <= 0) continue;
+    const T* C = c.g + G_CON + 16 * ci;
+    T sgn = sb == b2 ? T(-1) : T(1), ray[3] = {sgn * C[4], sgn * C[5], sgn * C[6]};
+    if (ray_hits_cylinder(spos, smat, m.touch_size, C + 1, ray)) sum += fn;
+  }
+  return warp_sum(sum);
+}
+
+}  // namespace adroit

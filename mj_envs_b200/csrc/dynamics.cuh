@@ -1,0 +1,419 @@
+// dynamics.cuh — warp-cooperative smooth dynamics for one environment:
+// level-synchronous forward kinematics, composite-rigid-body mass matrix, recursive Newton-Euler bias forces,
+// affine actuation, packed Cholesky factorisation / solves and M^-1.
+//
+// Reference semantics: MuJoCo 2.1 mj_kinematics / mj_crb / mj_rne / mj_fwdActuation / mj_fwdAcceleration as reached
+// from the reference through MujocoEnv.do_simulation (hammer_v0.py:60, door_v0.py:61, pen_v0.py:73,
+// relocate_v0.py:52) -- third-party code, restated from the published algorithm.
+//
+// fp32 design note: every spatial quantity of body b is expressed in world axes about the body's OWN origin
+// xpos[b]; parent<->child transfers are pure translations by xpos[child]-xpos[parent].  Lever arms therefore stay
+// at link scale and the tiny finger inertias (1e-5 kg m^2) are never buried under parallel-axis terms of a far
+// away reference point, which a single global origin would do in fp32.
+#pragma once
+#include "model.cuh"
+
+namespace adroit {
+
+template <typename T> struct Ctx {
+  const DModel<T>& m;
+  T* s;      // shared memory slice (T)
+  int* si;   // shared memory slice (int)
+  T* g;      // global scratch of this env
+  int* gi;   // int scratch of this env
+  int lane;
+  int ncon, nsimple;
+  __device__ Ctx(const DModel<T>& mm, T* s_, int* si_, T* g_, int* gi_, int lane_)
+      : m(mm), s(s_), si(si_), g(g_), gi(gi_), lane(lane_), ncon(0), nsimple(0) {}
+  DI T* v(int k) const { return s + k * NVP; }
+};
+
+template <typename T> DI void quat_mul(T* r, const T* a, const T* b) {
+  T w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  T x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  T y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  T z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  r[0] = w; r[1] = x; r[2] = y; r[3] = z;
+}
+template <typename T> DI void quat_norm(T* q) {
+  T n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  if (n < tiny<T>()) { q[0] = 1; q[1] = q[2] = q[3] = 0; return; }
+  T inv = T(1) / n;
+  q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv;
+}
+template <typename T> DI void quat2mat(T* R, const T* q) {
+  T w = q[0], x = q[1], y = q[2], z = q[3];
+  R[0] = w * w + x * x - y * y - z * z; R[1] = 2 * (x * y - w * z); R[2] = 2 * (x * z + w * y);
+  R[3] = 2 * (x * y + w * z); R[4] = w * w - x * x + y * y - z * z; R[5] = 2 * (y * z - w * x);
+  R[6] = 2 * (x * z - w * y); R[7] = 2 * (y * z + w * x); R[8] = w * w - x * x - y * y + z * z;
+}
+template <typename T> DI void rot(T* r, const T* R, const T* v) {
+  T x = R[0] * v[0] + R[1] * v[1] + R[2] * v[2], y = R[3] * v[0] + R[4] * v[1] + R[5] * v[2], z = R[6] * v[0] + R[7] * v[1] + R[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <typename T> DI void cross3(T* r, const T* a, const T* b) {
+  T x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+template <typename T> DI T dot3(const T* a, const T* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+template <typename T> DI void sincos_t(T x, T* s, T* c);
+template <> DI void sincos_t<float>(float x, float* s, float* c) { sincosf(x, s, c); }
+template <> DI void sincos_t<double>(double x, double* s, double* c) { sincos(x, s, c); }
+
+// ---------------------------------------------------------------- kinematics (level-synchronous over the body tree)
+template <typename T> __device__ __noinline__ void kinematics(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  T *xpos = c.s + O_XPOS, *xquat = c.s + O_XQUAT, *xmat = c.s + O_XMAT, *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS;
+  const T *par = c.s + O_PAR, *qpos = c.v(V_QPOS);
+  if (c.lane == 0) {
+    xpos[0] = xpos[1] = xpos[2] = 0;
+    xquat[0] = 1; xquat[1] = xquat[2] = xquat[3] = 0;
+    for (int i = 0; i < 9; i++) xmat[i] = (i % 4 == 0) ? T(1) : T(0);
+  }
+  __syncwarp();
+  for (int L = 1; L < m.nlevel; L++) {
+    int beg = m.level_start[L], end = m.level_start[L + 1];
+    for (int idx = beg + c.lane; idx < end; idx += 32) {
+      int b = m.level_body[idx], p = m.body_parent[b];
+      T bp[3], bq[4], pos[3], quat[4], R[9], t[3];
+      int po = m.body_par[2 * b], qo = m.body_par[2 * b + 1];
+      for (int i = 0; i < 3; i++) bp[i] = po >= 0 ? par[po + i] : m.body_pos[3 * b + i];
+      for (int i = 0; i < 4; i++) bq[i] = qo >= 0 ? par[qo + i] : m.body_quat[4 * b + i];
+      quat_norm(bq);
+      rot(t, xmat + 9 * p, bp);
+      for (int i = 0; i < 3; i++) pos[i] = xpos[3 * p + i] + t[i];
+      quat_mul(quat, xquat + 4 * p, bq);
+      int ja = m.body_jntadr[b], jn = m.body_jntnum[b];
+      for (int k = 0; k < jn; k++) {
+        int j = ja + k;
+        quat2mat(R, quat);
+        rot(t, R, m.jnt_pos + 3 * j);
+        for (int i = 0; i < 3; i++) xanc[3 * j + i] = pos[i] + t[i];
+        T ax[3];
+        rot(ax, R, m.jnt_axis + 3 * j);
+        for (int i = 0; i < 3; i++) xaxis[3 * j + i] = ax[i];
+        if (m.jnt_type[j] == J_SLIDE) {
+          for (int i = 0; i < 3; i++) pos[i] += ax[i] * qpos[j];
+        } else {
+          T sn, cs;
+          sincos_t(T(0.5) * qpos[j], &sn, &cs);
+          T qj[4] = {cs, sn * m.jnt_axis[3 * j], sn * m.jnt_axis[3 * j + 1], sn * m.jnt_axis[3 * j + 2]};
+          quat_mul(quat, quat, qj);
+          quat2mat(R, quat);
+          rot(t, R, m.jnt_pos + 3 * j);
+          for (int i = 0; i < 3; i++) pos[i] = xanc[3 * j + i] - t[i];
+        }
+      }
+      quat_norm(quat);
+      quat2mat(R, quat);
+      for (int i = 0; i < 3; i++) xpos[3 * b + i] = pos[i];
+      for (int i = 0; i < 4; i++) xquat[4 * b + i] = quat[i];
+      for (int i = 0; i < 9; i++) xmat[9 * b + i] = R[i];
+    }
+    __syncwarp();
+  }
+}
+
+// geom / site world frames (global scratch) and single-body inertias about the body origin
+template <typename T> __device__ __noinline__ void frames_and_inertia(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  const T *xpos = c.s + O_XPOS, *xmat = c.s + O_XMAT, *par = c.s + O_PAR;
+  for (int g = c.lane; g < m.ngeom; g += 32) {
+    int b = m.geom_body[g];
+    T t[3];
+    rot(t, xmat + 9 * b, m.geom_pos + 3 * g);
+    for (int i = 0; i < 3; i++) c.g[G_GPOS + 3 * g + i] = xpos[3 * b + i] + t[i];
+    const T *A = xmat + 9 * b, *B = m.geom_mat + 9 * g;
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) c.g[G_GMAT + 9 * g + 3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+  }
+  for (int sidx = c.lane; sidx < m.nsite; sidx += 32) {
+    int b = m.site_body[sidx], so = m.site_par[sidx];
+    T sp[3], t[3];
+    for (int i = 0; i < 3; i++) sp[i] = so >= 0 ? par[so + i] : m.site_pos[3 * sidx + i];
+    rot(t, xmat + 9 * b, sp);
+    for (int i = 0; i < 3; i++) c.g[G_SPOS + 3 * sidx + i] = xpos[3 * b + i] + t[i];
+  }
+  // inertia {m, h[3] = m*c, I[6] = xx,yy,zz,xy,xz,yz} about xpos[b], world axes
+  T* crb = c.s + O_CRB;
+  for (int b = c.lane; b < m.nbody; b += 32) {
+    T mass = m.body_mass[b], Rw[9], cv[3];
+    const T *A = xmat + 9 * b, *B = m.body_imat + 9 * b, *dg = m.body_inertia + 3 * b;
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) Rw[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+    rot(cv, A, m.body_ipos + 3 * b);
+    T cc = dot3(cv, cv);
+    T I[6];
+    const int ii[6] = {0, 1, 2, 0, 0, 1}, jj[6] = {0, 1, 2, 1, 2, 2};
+    for (int e = 0; e < 6; e++) {
+      int i = ii[e], j = jj[e];
+      T v = Rw[3 * i] * dg[0] * Rw[3 * j] + Rw[3 * i + 1] * dg[1] * Rw[3 * j + 1] + Rw[3 * i + 2] * dg[2] * Rw[3 * j + 2];
+      v += mass * ((i == j ? cc : T(0)) - cv[i] * cv[j]);
+      I[e] = v;
+    }
+    T out[10] = {mass, mass * cv[0], mass * cv[1], mass * cv[2], I[0], I[1], I[2], I[3], I[4], I[5]};
+    for (int e = 0; e < 10; e++) { crb[10 * b + e] = out[e]; c.g[G_CIN + 10 * b + e] = out[e]; }
+  }
+  __syncwarp();
+}
+
+// (n, f) = I * (w, v) for an inertia stored as {m, h, Ixx, Iyy, Izz, Ixy, Ixz, Iyz}
+template <typename T> DI void inert_mul(T* out, const T* I, const T* mv) {
+  const T* h = I + 1;
+  T t[3];
+  out[0] = I[4] * mv[0] + I[7] * mv[1] + I[8] * mv[2];
+  out[1] = I[7] * mv[0] + I[5] * mv[1] + I[9] * mv[2];
+  out[2] = I[8] * mv[0] + I[9] * mv[1] + I[6] * mv[2];
+  cross3(t, h, mv + 3);
+  out[0] += t[0]; out[1] += t[1]; out[2] += t[2];
+  cross3(t, h, mv);
+  out[3] = I[0] * mv[3] - t[0]; out[4] = I[0] * mv[4] - t[1]; out[5] = I[0] * mv[5] - t[2];
+}
+// motion vector of dof j about origin O (world axes)
+template <typename T> DI void dof_motion(const DModel<T>& m, const T* xanc, const T* xaxis, int j, const T* O, T* S) {
+  const T* a = xaxis + 3 * j;
+  if (m.jnt_type[j] == J_SLIDE) {
+    S[0] = S[1] = S[2] = 0;
+    S[3] = a[0]; S[4] = a[1]; S[5] = a[2];
+  } else {
+    T r[3] = {xanc[3 * j] - O[0], xanc[3 * j + 1] - O[1], xanc[3 * j + 2] - O[2]};
+    S[0] = a[0]; S[1] = a[1]; S[2] = a[2];
+    cross3(S + 3, r, a);
+  }
+}
+
+// composite inertias (children folded into parents, deepest level first) and the joint-space inertia matrix
+template <typename T> __device__ __noinline__ void mass_matrix(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  T *crb = c.s + O_CRB, *M = c.s + O_M;
+  const T *xpos = c.s + O_XPOS, *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS;
+  for (int L = m.nlevel - 1; L >= 1; L--) {
+    int beg = m.level_start[L - 1], end = m.level_start[L];
+    for (int idx = beg + c.lane; idx < end; idx += 32) {
+      int p = m.level_body[idx];
+      if (p == 0) continue;  // the world body's composite is never used
+      T acc[10];
+      for (int e = 0; e < 10; e++) acc[e] = crb[10 * p + e];
+      for (int k = m.child_start[p]; k < m.child_start[p + 1]; k++) {
+        int ch = m.child_list[k];
+        const T* I = crb + 10 * ch;
+        T r[3] = {xpos[3 * ch] - xpos[3 * p], xpos[3 * ch + 1] - xpos[3 * p + 1], xpos[3 * ch + 2] - xpos[3 * p + 2]};
+        T mass = I[0], hr = I[1] * r[0] + I[2] * r[1] + I[3] * r[2], rr = dot3(r, r);
+        T diag = 2 * hr + mass * rr;
+        acc[0] += mass;
+        acc[1] += I[1] + mass * r[0]; acc[2] += I[2] + mass * r[1]; acc[3] += I[3] + mass * r[2];
+        acc[4] += I[4] + diag - (2 * I[1] * r[0] + mass * r[0] * r[0]);
+        acc[5] += I[5] + diag - (2 * I[2] * r[1] + mass * r[1] * r[1]);
+        acc[6] += I[6] + diag - (2 * I[3] * r[2] + mass * r[2] * r[2]);
+        acc[7] += I[7] - (I[1] * r[1] + r[0] * I[2] + mass * r[0] * r[1]);
+        acc[8] += I[8] - (I[1] * r[2] + r[0] * I[3] + mass * r[0] * r[2]);
+        acc[9] += I[9] - (I[2] * r[2] + r[1] * I[3] + mass * r[1] * r[2]);
+      }
+      for (int e = 0; e < 10; e++) crb[10 * p + e] = acc[e];
+    }
+    __syncwarp();
+  }
+  for (int p = c.lane; p < NTRI; p += 32) M[p] = 0;
+  __syncwarp();
+  for (int i = c.lane; i < m.nv; i += 32) {
+    int b = m.dof_body[i];
+    const T* O = xpos + 3 * b;
+    T S[6], F[6];
+    dof_motion(m, xanc, xaxis, i, O, S);
+    inert_mul(F, crb + 10 * b, S);
+    M[tri(i, i)] = dot3(S, F) + dot3(S + 3, F + 3) + m.dof_armature[i];
+    for (int j = m.dof_parent[i]; j >= 0; j = m.dof_parent[j]) {
+      T Sj[6];
+      dof_motion(m, xanc, xaxis, j, O, Sj);
+      M[tri(i, j)] = dot3(Sj, F) + dot3(Sj + 3, F + 3);
+    }
+  }
+  __syncwarp();
+}
+
+// recursive Newton-Euler: bias forces (Coriolis + centrifugal + gravity) into V_T1
+template <typename T> __device__ __noinline__ void rne_bias(Ctx<T>& c) {
+  const DModel<T>& m = c.m;
+  const T *xpos = c.s + O_XPOS, *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS, *qvel = c.v(V_QVEL);
+  T *vel = c.g + G_VEL, *acc = c.g + G_ACC, *frc = c.g + G_FRC;
+  if (c.lane == 0) {
+    for (int i = 0; i < 6; i++) { vel[i] = 0; frc[i] = 0; }
+    acc[0] = acc[1] = acc[2] = 0;
+    acc[3] = -m.gravity[0]; acc[4] = -m.gravity[1]; acc[5] = -m.gravity[2];
+  }
+  __syncwarp();
+  for (int L = 1; L < m.nlevel; L++) {
+    int beg = m.level_start[L], end = m.level_start[L + 1];
+    for (int idx = beg + c.lane; idx < end; idx += 32) {
+      int b = m.level_body[idx], p = m.body_parent[b];
+      const T* O = xpos + 3 * b;
+      T r[3] = {O[0] - xpos[3 * p], O[1] - xpos[3 * p + 1], O[2] - xpos[3 * p + 2]};
+      T v[6], a[6], t[3];
+      for (int i = 0; i < 6; i++) { v[i] = vel[6 * p + i]; a[i] = acc[6 * p + i]; }
+      cross3(t, v, r);
+      v[3] += t[0]; v[4] += t[1]; v[5] += t[2];
+      cross3(t, a, r);
+      a[3] += t[0]; a[4] += t[1]; a[5] += t[2];
+      int ja = m.body_jntadr[b], jn = m.body_jntnum[b];
+      for (int k = 0; k < jn; k++) {
+        int j = ja + k;
+        T S[6], vj[6], u[3], w[3];
+        dof_motion(m, xanc, xaxis, j, O, S);
+        for (int i = 0; i < 6; i++) vj[i] = S[i] * qvel[j];
+        cross3(t, v, vj);              // w x w'
+        cross3(u, v, vj + 3);          // w x v'
+        cross3(w, v + 3, vj);          // v x w'
+        a[0] += t[0]; a[1] += t[1]; a[2] += t[2];
+        a[3] += u[0] + w[0]; a[4] += u[1] + w[1]; a[5] += u[2] + w[2];
+        for (int i = 0; i < 6; i++) v[i] += vj[i];
+      }
+      for (int i = 0; i < 6; i++) { vel[6 * b + i] = v[i]; acc[6 * b + i] = a[i]; }
+      const T* I = c.g + G_CIN + 10 * b;
+      T Ia[6], Iv[6], f[6], u[3];
+      inert_mul(Ia, I, a);
+      inert_mul(Iv, I, v);
+      cross3(t, v, Iv);          // w x n
+      cross3(u, v + 3, Iv + 3);  // v x f
+      f[0] = Ia[0] + t[0] + u[0]; f[1] = Ia[1] + t[1] + u[1]; f[2] = Ia[2] + t[2] + u[2];
+      cross3(t, v, Iv + 3);      // w x f
+      f[3] = Ia[3] + t[0]; f[4] = Ia[4] + t[1]; f[5] = Ia[5] + t[2];
+      for (int i = 0; i < 6; i++) frc[6 * b + i] = f[i];
+    }
+    __syncwarp();
+  }
+  for (int L = m.nlevel - 1; L >= 2; L--) {
+    int beg = m.level_start[L - 1], end = m.level_start[L];
+    for (int idx = beg + c.lane; idx < end; idx += 32) {
+      int p = m.level_body[idx];
+      T f[6];
+      for (int i = 0; i < 6; i++) f[i] = frc[6 * p + i];
+      for (int k = m.child_start[p]; k < m.child_start[p + 1]; k++) {
+        int ch = m.child_list[k];
+        T r[3] = {xpos[3 * ch] - xpos[3 * p], xpos[3 * ch + 1] - xpos[3 * p + 1], xpos[3 * ch + 2] - xpos[3 * p + 2]};
+        T t[3];
+        cross3(t, r, frc + 6 * ch + 3);
+        for (int i = 0; i < 3; i++) { f[i] += frc[6 * ch + i] + t[i]; f[3 + i] += frc[6 * ch + 3 + i]; }
+      }
+      for (int i = 0; i < 6; i++) frc[6 * p + i] = f[i];
+    }
+    __syncwarp();
+  }
+  T* bias = c.v(V_T1);
+  for (int j = c.lane; j < m.nv; j += 32) {
+    int b = m.dof_body[j];
+    T S[6];
+    dof_motion(m, xanc, xaxis, j, xpos + 3 * b, S);
+    bias[j] = dot3(S, frc + 6 * b) + dot3(S + 3, frc + 6 * b + 3);
+  }
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------- packed dense linear algebra on the warp
+// in-place Cholesky A = L L^T of a packed lower-triangular n x n matrix (left-looking by columns)
+template <typename T> __device__ __noinline__ void chol_packed(T* A, int n, int lane) {
+  for (int j = 0; j < n; j++) {
+    T s0 = 0, s1 = 0;
+    int i0 = j + lane, i1 = j + lane + 32;
+    const T* Lj = A + tri(j, 0);
+    if (i0 < n) {
+      const T* Li = A + tri(i0, 0);
+      s0 = Li[j];
+      for (int k = 0; k < j; k++) s0 -= Li[k] * Lj[k];
+    }
+    if (i1 < n) {
+      const T* Li = A + tri(i1, 0);
+      s1 = Li[j];
+      for (int k = 0; k < j; k++) s1 -= Li[k] * Lj[k];
+    }
+    T d = warp_bcast(s0, 0);
+    d = sqrt(d > tiny<T>() ? d : tiny<T>());
+    T inv = T(1) / d;
+    __syncwarp();
+    if (i0 < n) A[tri(i0, j)] = lane == 0 ? d : s0 * inv;
+    if (i1 < n) A[tri(i1, j)] = s1 * inv;
+    __syncwarp();
+  }
+}
+// solve L L^T x = b in place (x, b in shared memory)
+template <typename T> __device__ __noinline__ void chol_solve_packed(const T* L, T* x, int n, int lane) {
+  for (int j = 0; j < n; j++) {
+    T xj = x[j] / L[tri(j, j)];
+    __syncwarp();
+    for (int i = j + 1 + lane; i < n; i += 32) x[i] -= L[tri(i, j)] * xj;
+    if (lane == 0) x[j] = xj;
+    __syncwarp();
+  }
+  for (int j = n - 1; j >= 0; j--) {
+    T xj = x[j] / L[tri(j, j)];
+    __syncwarp();
+    for (int i = lane; i < j; i += 32) x[i] -= L[tri(j, i)] * xj;
+    if (lane == 0) x[j] = xj;
+    __syncwarp();
+  }
+}
+// y = A x for a packed symmetric matrix
+template <typename T> DI void symv_packed(const T* A, const T* x, T* y, int n, int lane) {
+  for (int i = lane; i < n; i += 32) {
+    T s = 0;
+    const T* Ai = A + tri(i, 0);
+    for (int j = 0; j <= i; j++) s += Ai[j] * x[j];
+    for (int j = i + 1; j < n; j++) s += A[tri(j, i)] * x[j];
+    y[i] = s;
+  }
+}
+// M^-1 (packed, global) from the Cholesky factor L (packed, shared): Linv by columns, then Linv^T Linv
+template <typename T> __device__ __noinline__ void minv_from_chol(const T* L, T* Linv, T* Minv, int n, int lane) {
+  for (int col = lane; col < n; col += 32) {
+    Linv[tri(col, col)] = T(1) / L[tri(col, col)];
+    for (int i = col + 1; i < n; i++) {
+      T s = 0;
+      const T* Li = L + tri(i, 0);
+      for (int k = col; k < i; k++) s += Li[k] * Linv[tri(k, col)];
+      Linv[tri(i, col)] = -s / Li[i];
+    }
+  }
+  __syncwarp();
+  int ntri = (n * (n + 1)) / 2;
+  for (int p = lane; p < ntri; p += 32) {
+    // p -> (a, b), a >= b
+    int a = (int)((sqrtf(8.0f * p + 1.0f) - 1.0f) * 0.5f);
+    while (tri(a + 1, 0) <= p) a++;
+    while (tri(a, 0) > p) a--;
+    int b = p - tri(a, 0);
+    T s = 0;
+    for (int k = a; k < n; k++) s += Linv[tri(k, a)] * Linv[tri(k, b)];
+    Minv[p] = s;
+  }
+  __syncwarp();
+}
+template <typename T> DI T sym_get(const T* A, int i, int j) { return i >= j ? A[tri(i, j)] : A[tri(j, i)]; }
+
+// passive + actuation + qfrc_smooth + qacc_smooth; leaves L_M in O_H, M in O_M
+template <typename T> __device__ __noinline__ void smooth_dynamics(Ctx<T>& c, bool need_minv) {
+  const DModel<T>& m = c.m;
+  const T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL), *bias = c.v(V_T1), *ctrl = c.v(V_CTRL);
+  T *qfs = c.v(V_QFS), *qas = c.v(V_QAS), *act = c.v(V_T2);
+  for (int j = c.lane; j < m.nv; j += 32) act[j] = 0;
+  __syncwarp();
+  for (int u = c.lane; u < m.nu; u += 32) {
+    T cu = tclamp(ctrl[u], m.act_ctrlrange[2 * u], m.act_ctrlrange[2 * u + 1]);
+    int j = m.act_dof[u];
+    act[j] = m.act_gain[u] * cu + m.act_bias[3 * u] + m.act_bias[3 * u + 1] * qpos[j] + m.act_bias[3 * u + 2] * qvel[j];
+  }
+  __syncwarp();
+  for (int j = c.lane; j < m.nv; j += 32) {
+    T f = -m.dof_damping[j] * qvel[j] - bias[j] + act[j];
+    qfs[j] = f;
+    qas[j] = f;
+    c.g[G_DBG_BIAS + j] = bias[j];
+  }
+  T *M = c.s + O_M, *H = c.s + O_H;
+  int ntri = (m.nv * (m.nv + 1)) / 2;
+  for (int p = c.lane; p < ntri; p += 32) H[p] = M[p];
+  __syncwarp();
+  chol_packed(H, m.nv, c.lane);
+  chol_solve_packed(H, qas, m.nv, c.lane);
+  if (need_minv) minv_from_chol(H, c.g + G_LINV, c.g + G_MINV, m.nv, c.lane);
+}
+
+}  // namespace adroit

@@ -1,0 +1,137 @@
+// model.cuh — device-side model tables, per-warp shared-memory layout and per-env scratch layout.
+//
+// Layout principles: one warp advances one environment.  Small per-dof vectors, body frames, the
+// packed joint-space matrices (M and the Newton Hessian / Cholesky factor) and the per-row constraint scalars live
+// in the warp's slice of shared memory; wide or rarely touched arrays (geom frames, spatial velocities, contact
+// Jacobians, M^-1) live in a per-env global scratch block that stays L1/L2-resident while the warp works on it.
+#pragma once
+#include "geom.cuh"
+
+namespace adroit {
+
+constexpr int NVP = 40;        // padded dof count (Adroit scenes: 30..36)
+constexpr int NBP = 32;        // bodies (29..31)
+constexpr int NGP = 36;        // collidable geoms (26..33)
+constexpr int NSP = 32;        // sites (28..32)
+constexpr int MAXCON = 32;     // contacts kept per env (overflow is counted, see adroit_overflow)
+constexpr int CROWS = MAXCON * 4;  // contact-frame Jacobian rows: normal, 2 tangents, torsion
+constexpr int MAXSIMPLE = 96;  // friction-loss + joint-limit + tendon-limit rows
+constexpr int NTRI = 672;      // packed lower triangle of a 36x36 matrix (666) padded
+constexpr int NPARP = 8;       // per-env model parameters (board_pos | door_body_pos | target quat | obj pos + target pos)
+constexpr int NTF = 24;        // cached task frames (positions the observation / reward read)
+constexpr int WPB = 4;         // warps (= envs) per block
+constexpr int MAXSURV = 96;    // candidate pairs surviving the bounding-sphere cull
+
+enum { T_HAMMER = 0, T_DOOR = 1, T_PEN = 2, T_RELOCATE = 3 };
+enum { J_SLIDE = 2, J_HINGE = 3 };
+enum { S_FRICTION = 0, S_JLIMIT = 1, S_TLIMIT = 2 };
+
+// ---- shared memory (per warp), offsets in units of T
+enum {
+  V_QPOS = 0, V_QVEL, V_WARM, V_CTRL, V_QFS, V_QAS, V_QACC, V_MA, V_GRAD, V_SEARCH, V_MV, V_QFC, V_T1, V_T2, V_COUNT
+};
+constexpr int O_PAR = V_COUNT * NVP;
+constexpr int O_XPOS = O_PAR + NPARP;
+constexpr int O_XQUAT = O_XPOS + NBP * 3;
+constexpr int O_XMAT = O_XQUAT + NBP * 4;
+constexpr int O_XANC = O_XMAT + NBP * 9;
+constexpr int O_XAXIS = O_XANC + NVP * 3;
+constexpr int O_CRB = O_XAXIS + NVP * 3;
+constexpr int O_M = O_CRB + NBP * 10;
+constexpr int O_H = O_M + NTRI;
+constexpr int O_SD = O_H + NTRI;
+constexpr int O_SAREF = O_SD + MAXSIMPLE;
+constexpr int O_SFL = O_SAREF + MAXSIMPLE;
+constexpr int O_SFORCE = O_SFL + MAXSIMPLE;
+constexpr int O_AC = O_SFORCE + MAXSIMPLE;      // contact-frame acceleration  Jf * qacc   [MAXCON][4]
+constexpr int O_AV = O_AC + CROWS;              // contact-frame search dir    Jf * search [MAXCON][4]
+constexpr int O_CD = O_AV + CROWS;              // D of every edge of the contact
+constexpr int O_CMU = O_CD + MAXCON;            // mu[3] per contact
+constexpr int O_CAREFN = O_CMU + MAXCON * 3;    // reference acceleration, normal part
+constexpr int O_CBT = O_CAREFN + MAXCON;        // -B*mu_k*vt_k per tangent
+constexpr int O_EF = O_CBT + MAXCON * 3;        // edge forces [MAXCON][6]
+constexpr int O_W = O_EF + MAXCON * 6;          // per-contact Hessian weights [MAXCON][7]
+constexpr int O_TF = O_W + MAXCON * 7;
+constexpr int SM_T = O_TF + NTF;
+// ints
+constexpr int I_SINFO = 0;                      // simple rows: kind | id<<2 | (side>0)<<12 | state<<13
+constexpr int I_CDIM = I_SINFO + MAXSIMPLE;
+constexpr int I_CB1 = I_CDIM + MAXCON;
+constexpr int I_CB2 = I_CB1 + MAXCON;
+constexpr int I_SURV = I_CB2 + MAXCON;
+constexpr int SM_I = I_SURV + MAXSURV;
+
+template <typename T> constexpr size_t smem_per_warp() { return SM_T * sizeof(T) + SM_I * sizeof(int); }
+
+// ---- global scratch (per env), offsets in units of T
+constexpr int G_GPOS = 0;
+constexpr int G_GMAT = G_GPOS + NGP * 3;
+constexpr int G_SPOS = G_GMAT + NGP * 9;
+constexpr int G_CIN = G_SPOS + NSP * 3;          // single-body inertia about the body origin, world axes [NBP][10]
+constexpr int G_VEL = G_CIN + NBP * 10;
+constexpr int G_ACC = G_VEL + NBP * 6;
+constexpr int G_FRC = G_ACC + NBP * 6;
+constexpr int G_CON = G_FRC + NBP * 6;           // contacts [MAXCON][16]: dist, pos3, frame9, margin, -, -
+constexpr int G_JR = G_CON + MAXCON * 16;        // contact-frame Jacobian, row-major [CROWS][NVP]
+constexpr int G_JT = G_JR + CROWS * NVP;         // same, dof-major [NVP][CROWS]
+constexpr int G_LINV = G_JT + NVP * CROWS;       // inverse Cholesky factor of M (packed)
+constexpr int G_MINV = G_LINV + NTRI;            // M^-1 (packed)
+constexpr int G_YT = G_MINV + NTRI;              // M^-1 Jt_k^T for the noslip pass [MAXCON][3][NVP]
+constexpr int G_DBG = G_YT + MAXCON * 3 * NVP;   // debug dump: M packed | qfrc_bias | qfrc_smooth | qacc_smooth | qacc | qfrc_constraint
+constexpr int G_DBG_M = G_DBG, G_DBG_BIAS = G_DBG + NTRI, G_DBG_QFS = G_DBG_BIAS + NVP, G_DBG_QAS = G_DBG_QFS + NVP,
+              G_DBG_QACC = G_DBG_QAS + NVP, G_DBG_QFC = G_DBG_QACC + NVP, G_DBG_XPOS = G_DBG_QFC + NVP,
+              G_DBG_XQUAT = G_DBG_XPOS + NBP * 3, G_DBG_EF = G_DBG_XQUAT + NBP * 4;
+constexpr int G_TOTAL = ((G_DBG_EF + MAXCON * 6 + 31) / 32) * 32;
+// int scratch per env: ncon, nsimple, newton iterations, noslip sweeps, then contact ints [MAXCON][4]: geom1, geom2, dim, first edge
+constexpr int GI_NCON = 0, GI_NSIMPLE = 1, GI_NITER = 2, GI_NSLIP = 3, GI_CON = 4, GI_TOTAL = 4 + MAXCON * 4 + 28;
+
+template <typename T> struct DModel {
+  int nv, nbody, ngeom, nsite, nu, ntendon, npair, npar, obs_dim, frame_skip, task, horizon, nlevel, touch_site;
+  int iterations, noslip_iterations, mpr_iterations;
+  const int *body_parent, *body_jntadr, *body_jntnum, *body_par, *level_start, *level_body, *child_start, *child_list;
+  const unsigned long long* body_dofmask;
+  const T *body_pos, *body_quat, *body_ipos, *body_imat, *body_mass, *body_inertia, *body_invweight0;
+  const int *jnt_type, *jnt_limited, *dof_body, *dof_parent;
+  const T *jnt_pos, *jnt_axis, *jnt_range, *jnt_margin, *dof_damping, *dof_armature, *dof_frictionloss, *dof_invweight0;
+  const int *geom_type, *geom_body;
+  const T *geom_pos, *geom_mat, *geom_size, *geom_rbound;
+  const int *site_body, *site_par;
+  const T* site_pos;
+  const int *pair_geom, *pair_condim;
+  const T *pair_friction, *pair_margin;
+  const int *tendon_dof, *tendon_limited;
+  const T *tendon_coef, *tendon_range, *tendon_margin, *tendon_invweight0;
+  const int* act_dof;
+  const T *act_ctrlrange, *act_gain, *act_bias;
+  int task_int[16];
+  T par0[NPARP];
+  T touch_size[3];
+  T timestep, gravity[3], tolerance, noslip_tolerance, impratio, solref[2], solimp[5], mpr_tolerance, meaninertia;
+  T pen_len, tar_len;
+  int any_damping;
+};
+
+// persistent per-env state + I/O pointers handed to the kernels
+template <typename T> struct DState {
+  int n;
+  T *qpos, *qvel, *warm, *par, *tf, *scratch;   // [n][NVP] x3, [n][NPARP], [n][NTF], [n][G_TOTAL]
+  int* iscratch;                                // [n][GI_TOTAL]
+  int *t, *episode, *ep_goal;                   // [n]
+  T* ep_return;                                 // [n]
+  double* acc;                                  // [n][4]: sum return, #any-goal, #goal>thr, #episodes
+  unsigned long long* overflow;                 // [2]
+  unsigned long long seed;
+  long long env_off;
+  unsigned flags;
+};
+
+DI int tri(int i, int j) { return (i * (i + 1)) / 2 + j; }  // i >= j
+
+template <typename T> DI T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+template <typename T> DI T warp_bcast(T v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
+}  // namespace adroit
