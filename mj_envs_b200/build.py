@@ -16,7 +16,13 @@ def nvcc():
     return "nvcc"
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, defines=(), out=None):
+    """`defines`/`out` build an experiment variant (tools/ab.sh); the product library takes neither."""
+    if out or defines:
+        cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
+               "-Xcompiler", "-fPIC", "-o", out, SRC] + [f"-D{d}" for d in defines]
+        subprocess.check_call(cmd)
+        return out
     if not force and os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(d) for d in DEPS):
         return LIB
     cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
@@ -29,4 +35,6 @@ def build(force=False, verbose=False):
 
 if __name__ == "__main__":
     import sys
-    print(build(force="-f" in sys.argv, verbose="-v" in sys.argv))
+    defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
+    outs = [a[2:] for a in sys.argv[1:] if a.startswith("-o")]
+    print(build(force="-f" in sys.argv, verbose="-v" in sys.argv, defines=defs, out=outs[0] if outs else None))

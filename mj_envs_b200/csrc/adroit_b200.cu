@@ -18,47 +18,72 @@ namespace adroit {
 enum { MODE_STEP = 0, MODE_RESET = 1, MODE_FORWARD = 2 };
 
 // ---------------------------------------------------------------- device pipeline
-template <typename T> __device__ void forward(Ctx<T>& c, const DState<T>& st, int debug) {
+// Block-wide phase alignment: the warps of a block run the same pipeline stage at the same time, so that the
+// instruction working set of an SM is one stage, not WPB different places of a ~500 KB kernel (ncu r1a: 62 % of the
+// stall samples were "no instruction").  Every warp of the block must reach every PHASE() -- inactive warps skip the
+// work but not the barrier.
+#ifndef ADROIT_PHASE_SYNC
+#define ADROIT_PHASE_SYNC 1
+#endif
+#if ADROIT_PHASE_SYNC
+#define PHASE() __syncthreads()
+#else
+#define PHASE() __syncwarp()
+#endif
+
+template <typename T> __device__ __noinline__ void forward(Ctx<T>& c, const DState<T>& st, int debug, bool act) {
   const DModel<T>& m = c.m;
   const int nv = m.nv, lane = c.lane;
-  kinematics(c);
-  frames_and_inertia(c);
-  mass_matrix(c);
-  if (debug) {
-    int ntri = (nv * (nv + 1)) / 2;
-    for (int p = lane; p < ntri; p += 32) c.g[G_DBG_M + p] = c.s[O_M + p];
-  }
-  collision(c, st.overflow);
-  rne_bias(c);
-  const bool slip = m.noslip_iterations > 0;
-  smooth_dynamics(c, slip);
-  make_constraint(c, st.overflow);
-  newton(c);
-  T *qacc = c.v(V_QACC), *qfc = c.v(V_QFC);
-  if (slip) {
-    noslip(c);
-    constraint_force(c);
-    T* u = c.v(V_T1);
-    symv_packed(c.g + G_MINV, qfc, u, nv, lane);
-    __syncwarp();
-    for (int j = lane; j < nv; j += 32) qacc[j] = c.v(V_QAS)[j] + u[j];
-    __syncwarp();
-  }
-  T touch = touch_sensor(c);
-  cache_task_frames(c, touch);
-  if (lane == 0) { c.gi[GI_NCON] = c.ncon; c.gi[GI_NSIMPLE] = c.nsimple; }
-  if (debug) {
-    for (int j = lane; j < nv; j += 32) {
-      c.g[G_DBG_QFS + j] = c.v(V_QFS)[j];
-      c.g[G_DBG_QAS + j] = c.v(V_QAS)[j];
-      c.g[G_DBG_QACC + j] = qacc[j];
-      c.g[G_DBG_QFC + j] = qfc[j];
+  PHASE();
+  if (act) {
+    kinematics(c);
+    frames_and_inertia(c);
+    mass_matrix(c);
+    if (debug) {
+      int ntri = (nv * (nv + 1)) / 2;
+      for (int p = lane; p < ntri; p += 32) c.g[G_DBG_M + p] = c.s[O_M + p];
     }
-    for (int i = lane; i < 3 * m.nbody; i += 32) c.g[G_DBG_XPOS + i] = c.s[O_XPOS + i];
-    for (int i = lane; i < 4 * m.nbody; i += 32) c.g[G_DBG_XQUAT + i] = c.s[O_XQUAT + i];
-    for (int i = lane; i < 6 * MAXCON; i += 32) c.g[G_DBG_EF + i] = c.s[O_EF + i];
   }
-  __syncwarp();
+  PHASE();
+  if (act) collision(c, st.overflow);
+  PHASE();
+  const bool slip = m.noslip_iterations > 0;
+  if (act) {
+    rne_bias(c);
+    smooth_dynamics(c, slip);
+  }
+  PHASE();
+  if (act) make_constraint(c, st.overflow);
+  PHASE();
+  if (act) newton(c);
+  PHASE();
+  if (act) {
+    T *qacc = c.v(V_QACC), *qfc = c.v(V_QFC);
+    if (slip) {
+      noslip(c);
+      constraint_force(c);
+      T* u = c.v(V_T1);
+      symv_packed(c.g + G_MINV, qfc, u, nv, lane);
+      __syncwarp();
+      for (int j = lane; j < nv; j += 32) qacc[j] = c.v(V_QAS)[j] + u[j];
+      __syncwarp();
+    }
+    T touch = touch_sensor(c);
+    cache_task_frames(c, touch);
+    if (lane == 0) { c.gi[GI_NCON] = c.ncon; c.gi[GI_NSIMPLE] = c.nsimple; }
+    if (debug) {
+      for (int j = lane; j < nv; j += 32) {
+        c.g[G_DBG_QFS + j] = c.v(V_QFS)[j];
+        c.g[G_DBG_QAS + j] = c.v(V_QAS)[j];
+        c.g[G_DBG_QACC + j] = qacc[j];
+        c.g[G_DBG_QFC + j] = qfc[j];
+      }
+      for (int i = lane; i < 3 * m.nbody; i += 32) c.g[G_DBG_XPOS + i] = c.s[O_XPOS + i];
+      for (int i = lane; i < 4 * m.nbody; i += 32) c.g[G_DBG_XQUAT + i] = c.s[O_XQUAT + i];
+      for (int i = lane; i < 6 * MAXCON; i += 32) c.g[G_DBG_EF + i] = c.s[O_EF + i];
+    }
+    __syncwarp();
+  }
 }
 
 template <typename T> DI bool warp_bad(const T* x, int n, int lane) {
@@ -72,15 +97,23 @@ template <typename T> DI void zero_state(Ctx<T>& c) {
 }
 
 // mj_step: forward + semi-implicit Euler with implicit joint damping
-template <typename T> __device__ void substep(Ctx<T>& c, const DState<T>& st, int debug) {
+template <typename T> __device__ void substep(Ctx<T>& c, const DState<T>& st, int debug, bool act) {
   const DModel<T>& m = c.m;
   const int nv = m.nv, lane = c.lane;
-  if (warp_bad(c.v(V_QPOS), nv, lane) || warp_bad(c.v(V_QVEL), nv, lane)) zero_state(c);  // mj_checkPos / mj_checkVel
-  forward(c, st, debug);
-  if (warp_bad(c.v(V_QACC), nv, lane)) {  // mj_checkAcc
-    zero_state(c);
-    forward(c, st, debug);
+  if (act && (warp_bad(c.v(V_QPOS), nv, lane) || warp_bad(c.v(V_QVEL), nv, lane))) zero_state(c);  // mj_checkPos / mj_checkVel
+  forward(c, st, debug, act);
+  bool bad = act && warp_bad(c.v(V_QACC), nv, lane);  // mj_checkAcc
+#if ADROIT_PHASE_SYNC
+  bool any_bad = __syncthreads_or(bad);
+#else
+  bool any_bad = bad;
+#endif
+  if (any_bad) {
+    if (bad) zero_state(c);
+    forward(c, st, debug, bad);
   }
+  PHASE();
+  if (!act) return;
   T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL), *warm = c.v(V_WARM), *qacc = c.v(V_QACC), *x = c.v(V_T1);
   const T h = m.timestep;
   if (m.any_damping) {
@@ -119,9 +152,9 @@ template <typename T> __device__ void episode_finish(const DModel<T>& m, const D
 }
 
 // reset_model (hammer_v0.py:106-132, door_v0.py:103-119, pen_v0.py:115-132, relocate_v0.py:85-103) + mj_forward
-template <typename T> __device__ void reset_env(Ctx<T>& c, const DState<T>& st, int env, int debug) {
+template <typename T> __device__ void reset_env(Ctx<T>& c, const DState<T>& st, int env, int debug, bool act) {
   const DModel<T>& m = c.m;
-  if (c.lane == 0) {
+  if (act && c.lane == 0) {
     episode_finish(m, st, env);
     T par[NPARP];
     draw_params(m, st.seed, (unsigned long long)(st.env_off + env), (unsigned)st.episode[env], par);
@@ -131,9 +164,11 @@ template <typename T> __device__ void reset_env(Ctx<T>& c, const DState<T>& st, 
     st.ep_return[env] = 0;
     st.ep_goal[env] = 0;
   }
-  for (int j = c.lane; j < NVP; j += 32) c.v(V_CTRL)[j] = 0;
-  zero_state(c);
-  forward(c, st, debug);
+  if (act) {
+    for (int j = c.lane; j < NVP; j += 32) c.v(V_CTRL)[j] = 0;
+    zero_state(c);
+  }
+  forward(c, st, debug, act);
 }
 
 template <typename T>
@@ -142,59 +177,72 @@ __global__ void __launch_bounds__(WPB * 32) env_kernel(const __grid_constant__ D
                                                         uint8_t* goal, int debug) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int env = blockIdx.x * WPB + warp;
-  if (env >= st.n) return;
+  const int env_raw = blockIdx.x * WPB + warp;
+  const int env = env_raw < st.n ? env_raw : st.n - 1;   // out-of-range warps idle on a valid index (they only take part in barriers)
   T* s = reinterpret_cast<T*>(smem_raw) + (size_t)warp * SM_T;
   int* si = reinterpret_cast<int*>(smem_raw + (size_t)WPB * SM_T * sizeof(T)) + warp * SM_I;
   Ctx<T> c(m, s, si, st.scratch + (size_t)env * G_TOTAL, st.iscratch + (size_t)env * GI_TOTAL, lane);
-  if (mode == MODE_RESET && mask && !mask[env]) return;
+  const bool act = env_raw < st.n && !(mode == MODE_RESET && mask && !mask[env]);
 
   // stage the persistent state
-  for (int j = lane; j < NVP; j += 32) {
-    c.v(V_QPOS)[j] = st.qpos[(size_t)env * NVP + j];
-    c.v(V_QVEL)[j] = st.qvel[(size_t)env * NVP + j];
-    c.v(V_WARM)[j] = st.warm[(size_t)env * NVP + j];
-    c.v(V_CTRL)[j] = 0;
+  if (act) {
+    for (int j = lane; j < NVP; j += 32) {
+      c.v(V_QPOS)[j] = st.qpos[(size_t)env * NVP + j];
+      c.v(V_QVEL)[j] = st.qvel[(size_t)env * NVP + j];
+      c.v(V_WARM)[j] = st.warm[(size_t)env * NVP + j];
+      c.v(V_CTRL)[j] = st.ctrl[(size_t)env * NVP + j];   // data.ctrl persists between calls (MjSim semantics)
+    }
+    if (lane < NPARP) s[O_PAR + lane] = st.par[(size_t)env * NPARP + lane];
+    if (lane < NTF) s[O_TF + lane] = st.tf[(size_t)env * NTF + lane];
   }
-  if (lane < NPARP) s[O_PAR + lane] = st.par[(size_t)env * NPARP + lane];
-  if (lane < NTF) s[O_TF + lane] = st.tf[(size_t)env * NTF + lane];
   __syncwarp();
 
   if (mode == MODE_RESET) {
-    reset_env(c, st, env, debug);
+    reset_env(c, st, env, debug, act);
   } else if (mode == MODE_FORWARD) {
-    forward(c, st, debug);
+    forward(c, st, debug, act);
   } else {
     // action map: hammer_v0.py:55-59 (act_mid / act_rng :49-50)
-    for (int u = lane; u < m.nu; u += 32) {
-      T a = tclamp((T)action[(size_t)env * m.nu + u], T(-1), T(1));
-      T lo = m.act_ctrlrange[2 * u], hi = m.act_ctrlrange[2 * u + 1];
-      c.v(V_CTRL)[u] = T(0.5) * (lo + hi) + a * T(0.5) * (hi - lo);
-    }
+    if (act)
+      for (int u = lane; u < m.nu; u += 32) {
+        T a = tclamp((T)action[(size_t)env * m.nu + u], T(-1), T(1));
+        T lo = m.act_ctrlrange[2 * u], hi = m.act_ctrlrange[2 * u + 1];
+        c.v(V_CTRL)[u] = T(0.5) * (lo + hi) + a * T(0.5) * (hi - lo);
+      }
     __syncwarp();
-    for (int k = 0; k < m.frame_skip; k++) substep(c, st, debug);  // do_simulation
-    T r;
-    int g, dn;
-    task_reward(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, lane, r, g, dn);
-    int tnew = st.t[env] + 1;
-    bool trunc = (st.flags & ADROIT_AUTO_RESET) && tnew >= m.horizon;
-    bool reset_now = trunc || ((st.flags & ADROIT_AUTO_RESET) && (st.flags & ADROIT_RESET_ON_DONE) && dn);
-    if (lane == 0) {
-      st.t[env] = tnew;
-      st.ep_return[env] += r;
-      st.ep_goal[env] += g;
-      if (reward) reward[env] = (float)r;
-      if (goal) goal[env] = (uint8_t)g;
-      if (done) done[env] = (uint8_t)(dn || trunc);
+    for (int k = 0; k < m.frame_skip; k++) substep(c, st, debug, act);  // do_simulation
+    bool reset_now = false;
+    if (act) {
+      T r;
+      int g, dn;
+      task_reward(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, lane, r, g, dn);
+      int tnew = st.t[env] + 1;
+      bool trunc = (st.flags & ADROIT_AUTO_RESET) && tnew >= m.horizon;
+      reset_now = trunc || ((st.flags & ADROIT_AUTO_RESET) && (st.flags & ADROIT_RESET_ON_DONE) && dn);
+      if (lane == 0) {
+        st.t[env] = tnew;
+        st.ep_return[env] += r;
+        st.ep_goal[env] += g;
+        if (reward) reward[env] = (float)r;
+        if (goal) goal[env] = (uint8_t)g;
+        if (done) done[env] = (uint8_t)(dn || trunc);
+      }
+      __syncwarp();
     }
-    __syncwarp();
-    if (reset_now) reset_env(c, st, env, debug);
+#if ADROIT_PHASE_SYNC
+    bool any_reset = __syncthreads_or(reset_now);
+#else
+    bool any_reset = reset_now;
+#endif
+    if (any_reset) reset_env(c, st, env, debug, reset_now);
   }
+  if (!act) return;
   if (obs) write_obs(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, obs + (size_t)env * m.obs_dim, lane);
   for (int j = lane; j < NVP; j += 32) {
     st.qpos[(size_t)env * NVP + j] = c.v(V_QPOS)[j];
     st.qvel[(size_t)env * NVP + j] = c.v(V_QVEL)[j];
     st.warm[(size_t)env * NVP + j] = c.v(V_WARM)[j];
+    st.ctrl[(size_t)env * NVP + j] = c.v(V_CTRL)[j];
   }
   if (lane < NPARP) st.par[(size_t)env * NPARP + lane] = s[O_PAR + lane];
   if (lane < NTF) st.tf[(size_t)env * NTF + lane] = s[O_TF + lane];
@@ -440,6 +488,7 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
   };
   st.n = n;
   if (A((void**)&st.qpos, sizeof(T) * n * NVP) || A((void**)&st.qvel, sizeof(T) * n * NVP) || A((void**)&st.warm, sizeof(T) * n * NVP) ||
+      A((void**)&st.ctrl, sizeof(T) * n * NVP) ||
       A((void**)&st.par, sizeof(T) * n * NPARP) || A((void**)&st.tf, sizeof(T) * n * NTF) ||
       A((void**)&st.scratch, sizeof(T) * (size_t)n * G_TOTAL) || A((void**)&st.iscratch, sizeof(int) * (size_t)n * GI_TOTAL) ||
       A((void**)&st.t, sizeof(int) * n) || A((void**)&st.episode, sizeof(int) * n) || A((void**)&st.ep_goal, sizeof(int) * n) ||

@@ -36,6 +36,21 @@ template <typename T> DI void sol_KB(const DModel<T>& m, T& K, T& B) {
   B = T(2) / tmax(T(1e-15), dmax * tc);
 }
 
+// lower bound of the distance from a point (given relative to the geom centre, world axes) to the geom's surface
+template <typename T> DI T shape_lower_bound(int type, const T* R, const T* size, T px, T py, T pz) {
+  T lx = R[0] * px + R[3] * py + R[6] * pz, ly = R[1] * px + R[4] * py + R[7] * pz, lz = R[2] * px + R[5] * py + R[8] * pz;
+  if (type == G_BOX) {
+    T ex = tmax(tabs(lx) - size[0], T(0)), ey = tmax(tabs(ly) - size[1], T(0)), ez = tmax(tabs(lz) - size[2], T(0));
+    return sqrt(ex * ex + ey * ey + ez * ez);
+  }
+  if (type == G_CAPSULE || type == G_CYLINDER) {   // a cylinder lies inside the capsule of the same radius and half length
+    T ez = tmax(tabs(lz) - size[1], T(0));
+    return sqrt(lx * lx + ly * ly + ez * ez) - size[0];
+  }
+  if (type == G_SPHERE) return sqrt(lx * lx + ly * ly + lz * lz) - size[0];
+  return T(-1e30);
+}
+
 // ---------------------------------------------------------------- collision over the static candidate list
 template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned long long* overflow) {
   const DModel<T>& m = c.m;
@@ -56,6 +71,10 @@ template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned
       } else {
         T bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
         hit = !(dx * dx + dy * dy + dz * dz > bound * bound);
+        // second, tighter (still conservative) test: the other geom's bounding sphere against this geom's own shape
+        // (large boxes -- table, wall, door -- have bounding spheres that swallow the whole hand)
+        if (hit) hit = !(shape_lower_bound(m.geom_type[g1], gmat + 9 * g1, m.geom_size + 3 * g1, dx, dy, dz) > m.geom_rbound[g2] + margin);
+        if (hit) hit = !(shape_lower_bound(m.geom_type[g2], gmat + 9 * g2, m.geom_size + 3 * g2, -dx, -dy, -dz) > m.geom_rbound[g1] + margin);
       }
     }
     unsigned mask = __ballot_sync(0xffffffffu, hit);

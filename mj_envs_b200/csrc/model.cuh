@@ -19,7 +19,10 @@ constexpr int MAXSIMPLE = 96;  // friction-loss + joint-limit + tendon-limit row
 constexpr int NTRI = 672;      // packed lower triangle of a 36x36 matrix (666) padded
 constexpr int NPARP = 8;       // per-env model parameters (board_pos | door_body_pos | target quat | obj pos + target pos)
 constexpr int NTF = 24;        // cached task frames (positions the observation / reward read)
-constexpr int WPB = 4;         // warps (= envs) per block
+#ifndef ADROIT_WPB
+#define ADROIT_WPB 4
+#endif
+constexpr int WPB = ADROIT_WPB;  // warps (= envs) per block
 constexpr int MAXSURV = 96;    // candidate pairs surviving the bounding-sphere cull
 
 enum { T_HAMMER = 0, T_DOOR = 1, T_PEN = 2, T_RELOCATE = 3 };
@@ -114,7 +117,7 @@ template <typename T> struct DModel {
 // persistent per-env state + I/O pointers handed to the kernels
 template <typename T> struct DState {
   int n;
-  T *qpos, *qvel, *warm, *par, *tf, *scratch;   // [n][NVP] x3, [n][NPARP], [n][NTF], [n][G_TOTAL]
+  T *qpos, *qvel, *warm, *ctrl, *par, *tf, *scratch;   // [n][NVP] x4, [n][NPARP], [n][NTF], [n][G_TOTAL]
   int* iscratch;                                // [n][GI_TOTAL]
   int *t, *episode, *ep_goal;                   // [n]
   T* ep_return;                                 // [n]

@@ -24,7 +24,7 @@ from .mjcf import Model, load_compiled
 ENV_IDS = {"door-v0": "door", "hammer-v0": "hammer", "pen-v0": "pen", "relocate-v0": "relocate"}
 MAX_EPISODE_STEPS = {"door-v0": 200, "hammer-v0": 200, "pen-v0": 100, "relocate-v0": 200}  # mj_envs_vision/__init__.py:4-29
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libadroit_b200.so")
+_LIB_PATH = os.environ.get("ADROIT_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libadroit_b200.so")
 _abi = None
 
 
@@ -191,12 +191,10 @@ class AdroitVecEnv:
         (and over all ranks with one NCCL all-reduce when torch.distributed is initialised; eval.py:69-97 semantics)."""
         out = np.zeros(4)
         self.abi.check(self.abi.reduce_episode(self._h, int(flush_running), out.ctypes.data, self._stream()))
-        t = torch.from_numpy(out)
-        if all_reduce and torch.distributed.is_available() and torch.distributed.is_initialized():
-            t = t.to(self.device) if torch.distributed.get_backend() == "nccl" else t
-            torch.distributed.all_reduce(t)
-            t = t.cpu()
-        return t.numpy()
+        if all_reduce:
+            from .sharding import allreduce_stats
+            out = allreduce_stats(out, self.device)
+        return out
 
     # ------------------------------------------------------------------ introspection (parity tests)
     def frames(self):
