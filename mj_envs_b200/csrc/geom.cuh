@@ -361,17 +361,22 @@ __device__ __noinline__ bool mpr_penetration(const MprObj<T>& o1, const MprObj<T
   }
 }
 
+// The portal refinement is evaluated in fp64 in BOTH builds: for shallow (margin-level) penetrations near a cylinder rim
+// the portal that survives is decided by differences of ~1e-6-scale support values, and in fp32 the surviving portal --
+// hence the contact normal -- flips (measured on B200: every fp32 single-step error above 1e-3 in pen-v0 was an MPR
+// normal, tools/gpu_worst.py).  B200 runs fp64 at half the fp32 rate and MPR pairs are few after the broadphase.
 template <typename T>
 DI void c_mpr(ConOut<T>& o, T margin, int t1, V3<T> p1, const M3<T>& R1, V3<T> s1, int t2, V3<T> p2, const M3<T>& R2, V3<T> s2,
               int max_iter, T tol) {
-  MprObj<T> o1, o2;
-  o1.type = t1; o1.pos = p1; o1.R = R1; o1.size = s1; o1.margin = margin;
-  o2.type = t2; o2.pos = p2; o2.R = R2; o2.size = s2; o2.margin = margin;
-  T depth;
-  V3<T> dir, pos;
-  if (!mpr_penetration(o1, o2, max_iter, tol, depth, dir, pos)) return;
-  if (dot(dir, dir) < T(0.5)) return;
-  o.add(margin - depth, pos, dir, margin);
+  MprObj<double> o1, o2;
+  o1.type = t1; o1.pos = mk<double>(p1.x, p1.y, p1.z); o1.size = mk<double>(s1.x, s1.y, s1.z); o1.margin = margin;
+  o2.type = t2; o2.pos = mk<double>(p2.x, p2.y, p2.z); o2.size = mk<double>(s2.x, s2.y, s2.z); o2.margin = margin;
+  for (int e = 0; e < 9; e++) { o1.R.m[e] = R1.m[e]; o2.R.m[e] = R2.m[e]; }
+  double depth;
+  V3<double> dir, pos;
+  if (!mpr_penetration<double>(o1, o2, max_iter, (double)tol, depth, dir, pos)) return;
+  if (dot(dir, dir) < 0.5) return;
+  o.add(margin - (T)depth, mk<T>((T)pos.x, (T)pos.y, (T)pos.z), mk<T>((T)dir.x, (T)dir.y, (T)dir.z), margin);
 }
 
 template <typename T>

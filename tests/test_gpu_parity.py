@@ -63,9 +63,9 @@ def test_fp32_single_step_within_north_star_tolerance(task):
     eq, ev, er, eo = _single_step_errors(task, fp64=False)
     tol = 1e-4                                      # north_star: <= 1e-4 relative
     assert np.median(eq) < 1e-6 and np.median(ev) < 1e-5 and np.median(er) < 1e-6
-    assert (eq < tol).mean() >= 0.97, (eq < tol).mean()
-    assert (er < tol).mean() >= 0.97, (er < tol).mean()
-    assert (ev < tol).mean() >= 0.88, (ev < tol).mean()   # velocities see the contact discontinuities first (see header)
+    assert (eq < tol).mean() >= 0.995, (eq < tol).mean()
+    assert (er < tol).mean() >= 0.995, (er < tol).mean()
+    assert (ev < tol).mean() >= 0.99, (ev < tol).mean()   # velocities see the contact discontinuities first (see header)
 
 
 @pytest.mark.parametrize("task", TASKS)

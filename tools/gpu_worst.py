@@ -27,12 +27,36 @@ L = env.debug_layout()
 ora.reset(); env.reset()
 rng = np.random.default_rng(1)
 records = []
+import collections
+cls = collections.Counter(); nbig = 0; ntot = 0
 worst = (0.0, None)
 for t in range(args.steps):
     q, v, p = ora.get_state()
     w = ora.get_warmstart()
     env._set_raw_state(q, v, p); env.set_warmstart(w)
-    _, oncon, onefc, _ = ora.solver()
+    ora.set_state(q, v, p)                       # re-run the oracle's forward at this state (ctrl persists)
+    oqa, oncon, onefc, _ = ora.solver()
+    gqa, gncon, gnefc, _ = env.solver()          # forward at the same state and ctrl
+    eacc = np.abs(gqa - oqa).max(axis=1) / np.maximum(1.0, np.abs(oqa).max(axis=1))
+    gcon = env.debug_scratch(L["G_CON"], 16 * L["MAXCON"]).reshape(n, -1, 16)
+    gi_ = np.zeros((n, L["GI_TOTAL"]), dtype=np.int32)
+    env.abi.lib.adroit_debug_iscratch(env._h, gi_.ctypes.data, None)
+    for e in np.nonzero(eacc > 1e-3)[0]:
+        if gncon[e] != oncon[e]:
+            cls["ncon differs"] += 1
+            continue
+        oc = ora.contacts(e)
+        dn = np.abs(gcon[e, :gncon[e], 4:7] - oc[:, 4:7]).max(axis=1) if len(oc) else np.zeros(0)
+        dd = np.abs(gcon[e, :gncon[e], 0] - oc[:, 0]) if len(oc) else np.zeros(0)
+        if len(dn) and dn.max() > 1e-3:
+            k = int(np.argmax(dn))
+            g = gi_[e, L["GI_CON"] + 4 * k: L["GI_CON"] + 4 * k + 2]
+            cls["normal differs, types %s" % (tuple(int(model.A["geom_type"][x]) for x in g),)] += 1
+        elif len(dd) and dd.max() > 1e-5:
+            cls["dist differs"] += 1
+        else:
+            cls["solver (same contacts) ncon=%d iters=%d" % (gncon[e], gi_[e, 2])] += 1
+    nbig += int((eacc > 1e-3).sum()); ntot += n
     a = rng.uniform(-1, 1, (n, env.nu)).astype(np.float32)
     if t % 10 < 5:
         a[:] = a[:, :1] * 0 + rng.uniform(-1, 1, (1, env.nu)).astype(np.float32)   # correlated grasping motions
@@ -58,6 +82,7 @@ for lo, hi in [(0, 1), (1, 4), (4, 8), (8, 16), (16, 100)]:
         print(f"   ncon in [{lo},{hi}): count {int(sel.sum())}, median err {np.median(rec[sel, 0]):.2e}, max {rec[sel, 0].max():.2e}, "
               f">1e-4: {float((rec[sel, 0] > 1e-4).mean()):.3f}")
 
+print('forward qacc rel err > 1e-3:', nbig, 'of', ntot, dict(cls))
 # dig into the worst state
 W = worst[1]
 print(f"worst: err {worst[0]:.3e} at t={W['t']} env={W['e']}")
