@@ -40,8 +40,10 @@ template <typename T> __device__ __noinline__ void forward(Ctx<T>& c, const DSta
     frames_and_inertia(c);
     mass_matrix(c);
     if (debug) {
-      int ntri = (nv * (nv + 1)) / 2;
-      for (int p = lane; p < ntri; p += 32) c.g[G_DBG_M + p] = c.s[O_M + p];
+      for (int p = lane; p < nv * nv; p += 32) {   // exported as the plain packed lower triangle
+        int i = p / nv, j = p - i * nv;
+        if (j <= i) c.g[G_DBG_M + (i * (i + 1)) / 2 + j] = c.s[O_M + tri(i, j)];
+      }
     }
   }
   PHASE();
@@ -63,7 +65,7 @@ template <typename T> __device__ __noinline__ void forward(Ctx<T>& c, const DSta
       noslip(c);
       constraint_force(c);
       T* u = c.v(V_T1);
-      symv_packed(c.g + G_MINV, qfc, u, nv, lane);
+      symv(c.g + G_MINV, qfc, u, nv, lane);
       __syncwarp();
       for (int j = lane; j < nv; j += 32) qacc[j] = c.v(V_QAS)[j] + u[j];
       __syncwarp();
@@ -118,16 +120,15 @@ template <typename T> __device__ void substep(Ctx<T>& c, const DState<T>& st, in
   const T h = m.timestep;
   if (m.any_damping) {
     T *H = c.s + O_H, *M = c.s + O_M;
-    int ntri = (nv * (nv + 1)) / 2;
-    for (int p = lane; p < ntri; p += 32) H[p] = M[p];
+    for (int p = lane; p < NTRI; p += 32) H[p] = M[p];
     __syncwarp();
     for (int j = lane; j < nv; j += 32) {
       H[tri(j, j)] += h * m.dof_damping[j];
       x[j] = c.v(V_QFS)[j] + c.v(V_QFC)[j];
     }
     __syncwarp();
-    chol_packed(H, nv, lane);
-    chol_solve_packed(H, x, nv, lane);
+    ltdl_factor(m, H, c.v(V_DINV), lane);    // M + h*diag(damping) keeps the tree sparsity of M
+    ltdl_solve(H, c.v(V_DINV), x, nv, lane);
   } else {
     for (int j = lane; j < nv; j += 32) x[j] = qacc[j];
     __syncwarp();
@@ -184,6 +185,8 @@ __global__ void __launch_bounds__(WPB * 32) env_kernel(const __grid_constant__ D
   Ctx<T> c(m, s, si, st.scratch + (size_t)env * G_TOTAL, st.iscratch + (size_t)env * GI_TOTAL, lane);
   const bool act = env_raw < st.n && !(mode == MODE_RESET && mask && !mask[env]);
 
+  for (int j = lane; j < V_COUNT * NVP; j += 32) s[j] = 0;   // tails [nv, NVP) of every work vector stay zero (vector loads read them)
+  __syncwarp();
   // stage the persistent state
   if (act) {
     for (int j = lane; j < NVP; j += 32) {
@@ -436,6 +439,43 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
   PI(m.tendon_dof, B.ints("tendon_dof")); PI(m.tendon_limited, B.ints("tendon_limited"));
   PR(m.tendon_coef, B.reals("tendon_coef")); PR(m.tendon_range, B.reals("tendon_range")); PR(m.tendon_margin, B.reals("tendon_margin"));
   PR(m.tendon_invweight0, B.reals("tendon_invweight0"));
+  {  // tree-sparse factorisation schedules (dynamics.cuh: ltdl_factor / minv_tree)
+    auto dof_parent = B.ints("dof_parent");
+    int nv = m.nv;
+    std::vector<std::vector<int>> anc(nv);          // proper ancestors, nearest first
+    std::vector<int> depth(nv, 0);
+    for (int k = 0; k < nv; k++) {
+      for (int i = dof_parent[k]; i >= 0; i = dof_parent[i]) anc[k].push_back(i);
+      depth[k] = (int)anc[k].size();
+    }
+    std::vector<int> ld_start(nv + 1, 0), ld_pair, wl_pair, tri_ab;
+    for (int k = 0; k < nv; k++) {
+      ld_start[k] = (int)ld_pair.size();
+      for (size_t a = 0; a < anc[k].size(); a++)
+        for (size_t b = a; b < anc[k].size(); b++) ld_pair.push_back(anc[k][a] | (anc[k][b] << 8));   // i >= j
+    }
+    ld_start[nv] = (int)ld_pair.size();
+    int maxd = 0;
+    for (int k = 0; k < nv; k++) maxd = depth[k] > maxd ? depth[k] : maxd;
+    for (int L = 1; L <= maxd; L++) {               // W rows by depth; each level padded to whole warps
+      for (int k = 0; k < nv; k++)
+        if (depth[k] == L) for (int j : anc[k]) wl_pair.push_back(k | (j << 8));
+      while (wl_pair.size() % 32) wl_pair.push_back(-1);
+    }
+    m.n_wl = (int)wl_pair.size();
+    std::vector<unsigned char> lca((size_t)nv * nv, 255);
+    for (int a = 0; a < nv; a++)
+      for (int b = 0; b <= a; b++) {
+        tri_ab.push_back(a | (b << 8));
+        int x = a, y = b;
+        while (x != y && x >= 0 && y >= 0) { if (x > y) x = dof_parent[x]; else y = dof_parent[y]; }
+        unsigned char v = (x == y && x >= 0) ? (unsigned char)x : 255;
+        lca[(size_t)a * nv + b] = v; lca[(size_t)b * nv + a] = v;
+      }
+    m.n_tri = (int)tri_ab.size();
+    PI(m.ld_start, ld_start); PI(m.ld_pair, ld_pair); PI(m.wl_pair, wl_pair); PI(m.tri_ab, tri_ab);
+    fix.push_back({A.put(lca), (const void**)&m.lca});
+  }
   PI(m.act_dof, act_dof); PR(m.act_ctrlrange, B.reals("act_ctrlrange")); PR(m.act_gain, B.reals("act_gain")); PR(m.act_bias, B.reals("act_bias"));
   // stash offsets; pointers are patched once the arena is on the device
   for (auto& f : fix) *f.slot = (const void*)f.off;

@@ -436,8 +436,7 @@ template <typename T> DI void ls_eval(Ctx<T>& c, T alpha, const T* qacc, const T
 template <typename T> __device__ __noinline__ void build_hessian(Ctx<T>& c) {
   const DModel<T>& m = c.m;
   T *H = c.s + O_H, *M = c.s + O_M;
-  int ntri = (m.nv * (m.nv + 1)) / 2;
-  for (int p = c.lane; p < ntri; p += 32) H[p] = M[p];
+  for (int p = c.lane; p < NTRI; p += 32) H[p] = M[p];
   __syncwarp();
   const int* sinfo = c.si + I_SINFO;
   const T* sD = c.s + O_SD;
@@ -515,7 +514,7 @@ template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
     for (int j = lane; j < nv; j += 32) s += T(0.5) * (Maa[j] - qfs[j]) * (a[j] - qas[j]);
     return warp_sum(s);
   };
-  symv_packed(M, warm, Ma, nv, lane);
+  symv(M, warm, Ma, nv, lane);
   contact_frame_mul(c, warm, ac);
   __syncwarp();
   T cost_ws = constraint_update(c, warm, false) + gauss(warm, Ma);
@@ -525,7 +524,7 @@ template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
   bool use_ws = cost_ws < cost_sm;
   for (int j = lane; j < nv; j += 32) qacc[j] = use_ws ? warm[j] : qas[j];
   __syncwarp();
-  symv_packed(M, qacc, Ma, nv, lane);
+  symv(M, qacc, Ma, nv, lane);
   contact_frame_mul(c, qacc, ac);
   __syncwarp();
   T cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
@@ -541,9 +540,9 @@ template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
     g2 = warp_sum(g2);
     if (scale * sqrt(g2) < m.tolerance) break;
     build_hessian(c);
-    chol_packed(H, nv, lane);
-    chol_solve_packed(H, search, nv, lane);
-    symv_packed(M, search, Mv, nv, lane);
+    chol_dense(H, c.v(V_DINV), nv, lane);
+    chol_solve(H, c.v(V_DINV), search, nv, lane);
+    symv(M, search, Mv, nv, lane);
     contact_frame_mul(c, search, av);
     __syncwarp();
     // exact line search on the convex piecewise-quadratic: safeguarded Newton on f'(alpha)
@@ -593,7 +592,7 @@ template <typename T> __device__ __noinline__ void noslip(Ctx<T>& c) {
   const T *saref = c.s + O_SAREF, *sfl = c.s + O_SFL, *cmu = c.s + O_CMU, *cbt = c.s + O_CBT;
   T *sforce = c.s + O_SFORCE, *ef = c.s + O_EF;
   // u = M^-1 J^T f  (qfc holds J^T f from the last constraint_update)
-  symv_packed(Minv, qfc, u, nv, lane);
+  symv(Minv, qfc, u, nv, lane);
   // Yt[ci][k] = M^-1 Jt_k^T and K1 = 4 mu_k^2 Jt_k.Yt_k (kept in O_AV[ci*4+1+k])
   T* K1 = c.s + O_AV;
   for (int ci = 0; ci < c.ncon; ci++) {
@@ -602,13 +601,11 @@ template <typename T> __device__ __noinline__ void noslip(Ctx<T>& c) {
       const T* Jt = JR + (4 * ci + 1 + k) * NVP;
       for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
       __syncwarp();
+      T* Y = YT + (3 * ci + k) * NVP;
+      symv(Minv, tmp, Y, nv, lane);
+      __syncwarp();
       T dsum = 0;
-      for (int i = lane; i < nv; i += 32) {
-        T s = 0;
-        for (int j = 0; j < nv; j++) s += sym_get(Minv, i, j) * tmp[j];
-        YT[(3 * ci + k) * NVP + i] = s;
-        dsum += s * tmp[i];
-      }
+      for (int i = lane; i < nv; i += 32) dsum += Y[i] * tmp[i];
       dsum = warp_sum(dsum);
       if (lane == 0) K1[4 * ci + 1 + k] = 4 * cmu[3 * ci + k] * cmu[3 * ci + k] * dsum;
       __syncwarp();

@@ -308,87 +308,204 @@ template <typename T> __device__ __noinline__ void rne_bias(Ctx<T>& c) {
   __syncwarp();
 }
 
-// ---------------------------------------------------------------- packed dense linear algebra on the warp
-// in-place Cholesky A = L L^T of a packed lower-triangular n x n matrix (left-looking by columns)
-template <typename T> __device__ __noinline__ void chol_packed(T* A, int n, int lane) {
+// ---------------------------------------------------------------- small linear algebra on the warp
+// Storage: lower triangle, row-major, rows padded to multiples of 4 (model.cuh tri()).  n <= 36: lane i owns row i and
+// lanes 0..n-33 also own row i+32.  Right-hand sides live in two registers per lane (x0 = x[lane], x1 = x[lane+32])
+// and pivots are broadcast with shuffles, so the triangular sweeps issue ~5 instructions per column.
+template <typename T> struct Vec4 { T v[4]; };
+template <typename T> DI Vec4<T> ld4(const T* p);
+template <> DI Vec4<float> ld4<float>(const float* p) {
+  float4 t = *reinterpret_cast<const float4*>(p);
+  Vec4<float> r; r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w; return r;
+}
+template <> DI Vec4<double> ld4<double>(const double* p) {
+  double2 a = *reinterpret_cast<const double2*>(p), b = *reinterpret_cast<const double2*>(p + 2);
+  Vec4<double> r; r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y; return r;
+}
+template <typename T> DI T rsqrt_t(T d);
+template <> DI float rsqrt_t<float>(float d) { float y = rsqrtf(d); return y * (1.5f - 0.5f * d * y * y); }   // one Newton step: ~1 ulp
+template <> DI double rsqrt_t<double>(double d) { return 1.0 / sqrt(d); }
+template <typename T> DI T rcp_t(T d);
+template <> DI float rcp_t<float>(float d) { return 1.0f / d; }
+template <> DI double rcp_t<double>(double d) { return 1.0 / d; }
+
+template <typename T> DI void load_vec(const T* x, int n, int lane, T& x0, T& x1) {
+  x0 = lane < n ? x[lane] : T(0);
+  x1 = lane + 32 < n ? x[lane + 32] : T(0);
+}
+template <typename T> DI void store_vec(T* x, int n, int lane, T x0, T x1) {
+  if (lane < n) x[lane] = x0;
+  if (lane + 32 < n) x[lane + 32] = x1;
+}
+
+// for k = n-1..0: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[k][i] * xk for i < k      (row k of L is contiguous)
+template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+  for (int k = n - 1; k >= 0; k--) {
+    T xs = k < 32 ? x0 : x1;
+    if (SCALE) xs *= k < 32 ? d0 : d1;
+    T xk = __shfl_sync(0xffffffffu, xs, k & 31);
+    if (SCALE && lane == (k & 31)) { if (k < 32) x0 = xk; else x1 = xk; }
+    const T* row = L + rowoff(k);
+    if (lane < k) x0 -= row[lane] * xk;
+    if (k > 32 && lane + 32 < k) x1 -= row[lane + 32] * xk;
+  }
+}
+// for k = 0..n-1: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[i][k] * xk for i > k      (column k of L: one row per lane)
+template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+  const T *r0 = L + rowoff(lane), *r1 = L + rowoff(lane + 32);
+  for (int k = 0; k < n; k++) {
+    T xs = k < 32 ? x0 : x1;
+    if (SCALE) xs *= k < 32 ? d0 : d1;
+    T xk = __shfl_sync(0xffffffffu, xs, k & 31);
+    if (SCALE && lane == (k & 31)) { if (k < 32) x0 = xk; else x1 = xk; }
+    if (lane > k && lane < n) x0 -= r0[k] * xk;
+    if (lane + 32 > k && lane + 32 < n) x1 -= r1[k] * xk;
+  }
+}
+
+// in-place Cholesky A = L L^T (left-looking by columns, lane = row, vectorised dot products); dinv[j] = 1 / L[j][j]
+template <typename T> __device__ __noinline__ void chol_dense(T* A, T* dinv, int n, int lane) {
+  const int i0 = lane, i1 = lane + 32;
+  T *r0 = A + rowoff(i0), *r1 = A + rowoff(i1 < n ? i1 : 0);
+  const bool two = n > 32;
   for (int j = 0; j < n; j++) {
+    const T* rj = A + rowoff(j);
     T s0 = 0, s1 = 0;
-    int i0 = j + lane, i1 = j + lane + 32;
-    const T* Lj = A + tri(j, 0);
-    if (i0 < n) {
-      const T* Li = A + tri(i0, 0);
-      s0 = Li[j];
-      for (int k = 0; k < j; k++) s0 -= Li[k] * Lj[k];
+    int k = 0;
+    for (; k + 4 <= j; k += 4) {
+      Vec4<T> b = ld4(rj + k), a = ld4(r0 + k);
+      s0 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
+      if (two) {
+        Vec4<T> c = ld4(r1 + k);
+        s1 += c.v[0] * b.v[0] + c.v[1] * b.v[1] + c.v[2] * b.v[2] + c.v[3] * b.v[3];
+      }
     }
-    if (i1 < n) {
-      const T* Li = A + tri(i1, 0);
-      s1 = Li[j];
-      for (int k = 0; k < j; k++) s1 -= Li[k] * Lj[k];
+    for (; k < j; k++) {
+      T b = rj[k];
+      s0 += r0[k] * b;
+      if (two) s1 += r1[k] * b;
     }
-    T d = warp_bcast(s0, 0);
-    d = sqrt(d > tiny<T>() ? d : tiny<T>());
-    T inv = T(1) / d;
+    s0 = r0[j] - s0;      // lanes with i0 < j read a neighbouring row: harmless, never stored
+    s1 = r1[j] - s1;
+    T d = __shfl_sync(0xffffffffu, j < 32 ? s0 : s1, j & 31);
+    d = d > tiny<T>() ? d : tiny<T>();
+    T inv = rsqrt_t(d);
     __syncwarp();
-    if (i0 < n) A[tri(i0, j)] = lane == 0 ? d : s0 * inv;
-    if (i1 < n) A[tri(i1, j)] = s1 * inv;
+    if (i0 == j) { r0[j] = d * inv; dinv[j] = inv; }
+    else if (i0 > j && i0 < n) r0[j] = s0 * inv;
+    if (two && i1 < n) {
+      if (i1 == j) { r1[j] = d * inv; dinv[j] = inv; }
+      else if (i1 > j) r1[j] = s1 * inv;
+    }
     __syncwarp();
   }
 }
-// solve L L^T x = b in place (x, b in shared memory)
-template <typename T> __device__ __noinline__ void chol_solve_packed(const T* L, T* x, int n, int lane) {
-  for (int j = 0; j < n; j++) {
-    T xj = x[j] / L[tri(j, j)];
+// x <- (L L^T)^-1 x  (x in shared memory)
+template <typename T> DI void chol_solve(const T* L, const T* dinv, T* x, int n, int lane) {
+  T x0, x1, d0, d1;
+  load_vec(x, n, lane, x0, x1);
+  load_vec(dinv, n, lane, d0, d1);
+  sweep_cols_asc<T, true>(L, d0, d1, x0, x1, n, lane);
+  sweep_rows_desc<T, true>(L, d0, d1, x0, x1, n, lane);
+  store_vec(x, n, lane, x0, x1);
+  __syncwarp();
+}
+
+// Tree-sparse factorisation M = L^T D L of a matrix with the sparsity of the joint-space inertia (entry (k,i) non-zero
+// only if i is an ancestor dof of k): eliminating leaves first creates no fill-in (Featherstone; MuJoCo's mj_factorM
+// uses the same order).  One step per dof, its (ancestor, ancestor) pair updates spread over the lanes; the schedule
+// ld_start / ld_pair is built on the host.  On return: strict lower part = L, diagonal = D, dinv = 1/D.
+template <typename T> __device__ __noinline__ void ltdl_factor(const DModel<T>& m, T* A, T* dinv, int lane) {
+  const int n = m.nv;
+  for (int k = n - 1; k >= 0; k--) {
+    const T* rk = A + rowoff(k);
+    T dk = rk[k];
+    dk = dk > tiny<T>() ? dk : tiny<T>();
+    T inv = rcp_t(dk);
+    int beg = m.ld_start[k], end = m.ld_start[k + 1];
+    for (int p = beg + lane; p < end; p += 32) {
+      int ij = m.ld_pair[p], i = ij & 255, j = ij >> 8;
+      A[tri(i, j)] -= rk[i] * rk[j] * inv;
+    }
     __syncwarp();
-    for (int i = j + 1 + lane; i < n; i += 32) x[i] -= L[tri(i, j)] * xj;
-    if (lane == 0) x[j] = xj;
-    __syncwarp();
-  }
-  for (int j = n - 1; j >= 0; j--) {
-    T xj = x[j] / L[tri(j, j)];
-    __syncwarp();
-    for (int i = lane; i < j; i += 32) x[i] -= L[tri(j, i)] * xj;
-    if (lane == 0) x[j] = xj;
+    // row k: L[k][i] = A[k][i] / D[k] for every i < k (entries outside the ancestor pattern are zero and stay zero)
+    for (int i = lane; i < k; i += 32) A[rowoff(k) + i] = rk[i] * inv;
+    if (lane == 0) dinv[k] = inv;
     __syncwarp();
   }
 }
-// y = A x for a packed symmetric matrix
-template <typename T> DI void symv_packed(const T* A, const T* x, T* y, int n, int lane) {
-  for (int i = lane; i < n; i += 32) {
+// x <- (L^T D L)^-1 x  (x in shared memory)
+template <typename T> DI void ltdl_solve(const T* L, const T* dinv, T* x, int n, int lane) {
+  T x0, x1, d0, d1;
+  load_vec(x, n, lane, x0, x1);
+  load_vec(dinv, n, lane, d0, d1);
+  sweep_rows_desc<T, false>(L, d0, d1, x0, x1, n, lane);
+  x0 *= d0; x1 *= d1;
+  sweep_cols_asc<T, false>(L, d0, d1, x0, x1, n, lane);
+  store_vec(x, n, lane, x0, x1);
+  __syncwarp();
+}
+// M^-1 = W D^-1 W^T with W = L^-1 (unit lower, same ancestor pattern): W by depth levels (wl_pair, levels padded to
+// whole warps), then every entry of M^-1 as a short sum over the common ancestors of its two dofs (lca table).
+template <typename T> __device__ __noinline__ void minv_tree(const DModel<T>& m, const T* L, const T* dinv, T* W, T* Minv, int lane) {
+  for (int p = lane; p < NTRI; p += 32) { W[p] = 0; Minv[p] = 0; }
+  __syncwarp();
+  for (int base = 0; base < m.n_wl; base += 32) {
+    int kj = m.wl_pair[base + lane];
+    if (kj >= 0) {
+      int k = kj & 255, j = kj >> 8;
+      const T* rk = L + rowoff(k);
+      T acc = rk[j];
+      for (int i = m.dof_parent[k]; i > j; i = m.dof_parent[i]) acc += rk[i] * W[tri(i, j)];
+      W[tri(k, j)] = -acc;
+    }
+    __syncwarp();
+  }
+  for (int p = lane; p < m.n_tri; p += 32) {
+    int ab = m.tri_ab[p], a = ab & 255, b = ab >> 8;   // a >= b
+    int k = m.lca[a * m.nv + b];
     T s = 0;
-    const T* Ai = A + tri(i, 0);
-    for (int j = 0; j <= i; j++) s += Ai[j] * x[j];
-    for (int j = i + 1; j < n; j++) s += A[tri(j, i)] * x[j];
-    y[i] = s;
-  }
-}
-// M^-1 (packed, global) from the Cholesky factor L (packed, shared): Linv by columns, then Linv^T Linv
-template <typename T> __device__ __noinline__ void minv_from_chol(const T* L, T* Linv, T* Minv, int n, int lane) {
-  for (int col = lane; col < n; col += 32) {
-    Linv[tri(col, col)] = T(1) / L[tri(col, col)];
-    for (int i = col + 1; i < n; i++) {
-      T s = 0;
-      const T* Li = L + tri(i, 0);
-      for (int k = col; k < i; k++) s += Li[k] * Linv[tri(k, col)];
-      Linv[tri(i, col)] = -s / Li[i];
+    while (k != 255) {
+      T wa = k == a ? T(1) : W[tri(a, k)], wb = k == b ? T(1) : W[tri(b, k)];
+      s += wa * wb * dinv[k];
+      int pk = m.dof_parent[k];
+      k = pk < 0 ? 255 : pk;
     }
+    Minv[tri(a, b)] = s;
   }
   __syncwarp();
-  int ntri = (n * (n + 1)) / 2;
-  for (int p = lane; p < ntri; p += 32) {
-    // p -> (a, b), a >= b
-    int a = (int)((sqrtf(8.0f * p + 1.0f) - 1.0f) * 0.5f);
-    while (tri(a + 1, 0) <= p) a++;
-    while (tri(a, 0) > p) a--;
-    int b = p - tri(a, 0);
-    T s = 0;
-    for (int k = a; k < n; k++) s += Linv[tri(k, a)] * Linv[tri(k, b)];
-    Minv[p] = s;
+}
+
+// y = A x for a symmetric matrix (lower storage); x, y in shared memory, y != x
+template <typename T> __device__ __noinline__ void symv(const T* A, const T* x, T* y, int n, int lane) {
+  T y0 = 0, y1 = 0;
+  const int i0 = lane, i1 = lane + 32;
+  if (i0 < n) {
+    const T* r = A + rowoff(i0);
+    for (int k = 0; k <= i0; k += 4) {      // pad entries of the row are zero
+      Vec4<T> a = ld4(r + k), b = ld4(x + k);
+      y0 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
+    }
   }
-  __syncwarp();
+  if (i1 < n) {
+    const T* r = A + rowoff(i1);
+    for (int k = 0; k <= i1; k += 4) {
+      Vec4<T> a = ld4(r + k), b = ld4(x + k);
+      y1 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
+    }
+  }
+  for (int j = 1; j < n; j++) {             // transpose part: row j contributes A[j][i] x[j] to every i < j
+    const T* rj = A + rowoff(j);
+    T xj = x[j];
+    if (i0 < j) y0 += rj[i0] * xj;
+    if (j > 32 && i1 < j) y1 += rj[i1] * xj;
+  }
+  if (i0 < n) y[i0] = y0;
+  if (i1 < n) y[i1] = y1;
 }
 template <typename T> DI T sym_get(const T* A, int i, int j) { return i >= j ? A[tri(i, j)] : A[tri(j, i)]; }
 
-// passive + actuation + qfrc_smooth + qacc_smooth; leaves L_M in O_H, M in O_M
+// passive + actuation + qfrc_smooth + qacc_smooth (+ M^-1 for the noslip pass); M stays in O_M, O_H is scratch
 template <typename T> __device__ __noinline__ void smooth_dynamics(Ctx<T>& c, bool need_minv) {
   const DModel<T>& m = c.m;
   const T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL), *bias = c.v(V_T1), *ctrl = c.v(V_CTRL);
@@ -408,12 +525,11 @@ template <typename T> __device__ __noinline__ void smooth_dynamics(Ctx<T>& c, bo
     c.g[G_DBG_BIAS + j] = bias[j];
   }
   T *M = c.s + O_M, *H = c.s + O_H;
-  int ntri = (m.nv * (m.nv + 1)) / 2;
-  for (int p = c.lane; p < ntri; p += 32) H[p] = M[p];
+  for (int p = c.lane; p < NTRI; p += 32) H[p] = M[p];
   __syncwarp();
-  chol_packed(H, m.nv, c.lane);
-  chol_solve_packed(H, qas, m.nv, c.lane);
-  if (need_minv) minv_from_chol(H, c.g + G_LINV, c.g + G_MINV, m.nv, c.lane);
+  ltdl_factor(m, H, c.v(V_DINV), c.lane);
+  ltdl_solve(H, c.v(V_DINV), qas, m.nv, c.lane);
+  if (need_minv) minv_tree(m, H, c.v(V_DINV), c.g + G_LINV, c.g + G_MINV, c.lane);
 }
 
 }  // namespace adroit

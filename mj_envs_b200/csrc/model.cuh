@@ -16,7 +16,7 @@ constexpr int NSP = 32;        // sites (28..32)
 constexpr int MAXCON = 32;     // contacts kept per env (overflow is counted, see adroit_overflow)
 constexpr int CROWS = MAXCON * 4;  // contact-frame Jacobian rows: normal, 2 tangents, torsion
 constexpr int MAXSIMPLE = 96;  // friction-loss + joint-limit + tendon-limit rows
-constexpr int NTRI = 672;      // packed lower triangle of a 36x36 matrix (666) padded
+constexpr int NTRI = 720;      // lower triangle of a 36x36 matrix, rows padded to multiples of 4 (16-byte aligned rows, see tri())
 constexpr int NPARP = 8;       // per-env model parameters (board_pos | door_body_pos | target quat | obj pos + target pos)
 constexpr int NTF = 24;        // cached task frames (positions the observation / reward read)
 #ifndef ADROIT_WPB
@@ -31,7 +31,7 @@ enum { S_FRICTION = 0, S_JLIMIT = 1, S_TLIMIT = 2 };
 
 // ---- shared memory (per warp), offsets in units of T
 enum {
-  V_QPOS = 0, V_QVEL, V_WARM, V_CTRL, V_QFS, V_QAS, V_QACC, V_MA, V_GRAD, V_SEARCH, V_MV, V_QFC, V_T1, V_T2, V_COUNT
+  V_QPOS = 0, V_QVEL, V_WARM, V_CTRL, V_QFS, V_QAS, V_QACC, V_MA, V_GRAD, V_SEARCH, V_MV, V_QFC, V_T1, V_T2, V_DINV, V_COUNT
 };
 constexpr int O_PAR = V_COUNT * NVP;
 constexpr int O_XPOS = O_PAR + NPARP;
@@ -55,7 +55,8 @@ constexpr int O_CBT = O_CAREFN + MAXCON;        // -B*mu_k*vt_k per tangent
 constexpr int O_EF = O_CBT + MAXCON * 3;        // edge forces [MAXCON][6]
 constexpr int O_W = O_EF + MAXCON * 6;          // per-contact Hessian weights [MAXCON][7]
 constexpr int O_TF = O_W + MAXCON * 7;
-constexpr int SM_T = O_TF + NTF;
+constexpr int SM_T = ((O_TF + NTF + 3) / 4) * 4;
+static_assert(O_M % 4 == 0 && O_H % 4 == 0, "matrix rows must be 16-byte aligned");
 // ints
 constexpr int I_SINFO = 0;                      // simple rows: kind | id<<2 | (side>0)<<12 | state<<13
 constexpr int I_CDIM = I_SINFO + MAXSIMPLE;
@@ -90,7 +91,7 @@ constexpr int GI_NCON = 0, GI_NSIMPLE = 1, GI_NITER = 2, GI_NSLIP = 3, GI_CON = 
 
 template <typename T> struct DModel {
   int nv, nbody, ngeom, nsite, nu, ntendon, npair, npar, obs_dim, frame_skip, task, horizon, nlevel, touch_site;
-  int iterations, noslip_iterations, mpr_iterations;
+  int iterations, noslip_iterations, mpr_iterations, n_wl, n_tri;
   const int *body_parent, *body_jntadr, *body_jntnum, *body_par, *level_start, *level_body, *child_start, *child_list;
   const unsigned long long* body_dofmask;
   const T *body_pos, *body_quat, *body_ipos, *body_imat, *body_mass, *body_inertia, *body_invweight0;
@@ -105,6 +106,9 @@ template <typename T> struct DModel {
   const int *tendon_dof, *tendon_limited;
   const T *tendon_coef, *tendon_range, *tendon_margin, *tendon_invweight0;
   const int* act_dof;
+  // tree-sparse factorisation tables (host-built from dof_parent, see fill_model)
+  const int *ld_start, *ld_pair, *wl_pair, *tri_ab;   // [nv+1], [..] i|j<<8, [..] k|j<<8, [ntri_real] a|b<<8
+  const unsigned char* lca;                          // [nv*nv] deepest common ancestor-or-self dof, 255 = none
   const T *act_ctrlrange, *act_gain, *act_bias;
   int task_int[16];
   T par0[NPARP];
@@ -128,7 +132,10 @@ template <typename T> struct DState {
   unsigned flags;
 };
 
-DI int tri(int i, int j) { return (i * (i + 1)) / 2 + j; }  // i >= j
+// Symmetric / triangular matrices are stored as the lower triangle, row-major, with row i padded to 4*(i/4+1) entries:
+// every row starts 16-byte aligned (vector loads in the dot-product loops) and the pad entries are kept at ZERO.
+DI int rowoff(int i) { int g = i >> 2; return 4 * (g + 1) * (2 * g + (i & 3)); }
+DI int tri(int i, int j) { return rowoff(i) + j; }  // i >= j
 
 template <typename T> DI T warp_sum(T v) {
 #pragma unroll
