@@ -178,11 +178,16 @@ __global__ void __launch_bounds__(WPB * 32) env_kernel(const __grid_constant__ D
                                                         uint8_t* goal, int debug) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int env_raw = blockIdx.x * WPB + warp;
+  // persistent blocks: the grid is sized to what is resident at once and walks the env tiles, so the per-warp global
+  // scratch (G_TOTAL words) is one slot per RESIDENT warp -- it stays in L2 however many envs the handle owns
+  const int ntiles = (st.n + WPB - 1) / WPB;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  const int env_raw = tile * WPB + warp;
   const int env = env_raw < st.n ? env_raw : st.n - 1;   // out-of-range warps idle on a valid index (they only take part in barriers)
   T* s = reinterpret_cast<T*>(smem_raw) + (size_t)warp * SM_T;
   int* si = reinterpret_cast<int*>(smem_raw + (size_t)WPB * SM_T * sizeof(T)) + warp * SM_I;
-  Ctx<T> c(m, s, si, st.scratch + (size_t)env * G_TOTAL, st.iscratch + (size_t)env * GI_TOTAL, lane);
+  T* gscratch = debug ? st.dbg_scratch + (size_t)env * G_TOTAL : st.scratch + (size_t)(blockIdx.x * WPB + warp) * G_TOTAL;
+  Ctx<T> c(m, s, si, gscratch, st.iscratch + (size_t)env * GI_TOTAL, lane);
   const bool act = env_raw < st.n && !(mode == MODE_RESET && mask && !mask[env]);
 
   for (int j = lane; j < V_COUNT * NVP; j += 32) s[j] = 0;   // tails [nv, NVP) of every work vector stay zero (vector loads read them)
@@ -239,16 +244,19 @@ __global__ void __launch_bounds__(WPB * 32) env_kernel(const __grid_constant__ D
 #endif
     if (any_reset) reset_env(c, st, env, debug, reset_now);
   }
-  if (!act) return;
-  if (obs) write_obs(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, obs + (size_t)env * m.obs_dim, lane);
-  for (int j = lane; j < NVP; j += 32) {
-    st.qpos[(size_t)env * NVP + j] = c.v(V_QPOS)[j];
-    st.qvel[(size_t)env * NVP + j] = c.v(V_QVEL)[j];
-    st.warm[(size_t)env * NVP + j] = c.v(V_WARM)[j];
-    st.ctrl[(size_t)env * NVP + j] = c.v(V_CTRL)[j];
+  if (act) {
+    if (obs) write_obs(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, obs + (size_t)env * m.obs_dim, lane);
+    for (int j = lane; j < NVP; j += 32) {
+      st.qpos[(size_t)env * NVP + j] = c.v(V_QPOS)[j];
+      st.qvel[(size_t)env * NVP + j] = c.v(V_QVEL)[j];
+      st.warm[(size_t)env * NVP + j] = c.v(V_WARM)[j];
+      st.ctrl[(size_t)env * NVP + j] = c.v(V_CTRL)[j];
+    }
+    if (lane < NPARP) st.par[(size_t)env * NPARP + lane] = s[O_PAR + lane];
+    if (lane < NTF) st.tf[(size_t)env * NTF + lane] = s[O_TF + lane];
   }
-  if (lane < NPARP) st.par[(size_t)env * NPARP + lane] = s[O_PAR + lane];
-  if (lane < NTF) st.tf[(size_t)env * NTF + lane] = s[O_TF + lane];
+  __syncwarp();
+  }  // tile loop
 }
 
 template <typename T> __global__ void obs_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, float* obs) {
@@ -376,6 +384,7 @@ struct adroit_sim {
   uint8_t *d_done = nullptr, *d_goal = nullptr;
   double* d_out4 = nullptr;
   int64_t launches = 0;
+  int max_blocks = 0, nslots = 0;   // resident blocks of env_kernel on this device / scratch slots (= max_blocks * WPB)
 };
 
 namespace {
@@ -530,7 +539,7 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
   if (A((void**)&st.qpos, sizeof(T) * n * NVP) || A((void**)&st.qvel, sizeof(T) * n * NVP) || A((void**)&st.warm, sizeof(T) * n * NVP) ||
       A((void**)&st.ctrl, sizeof(T) * n * NVP) ||
       A((void**)&st.par, sizeof(T) * n * NPARP) || A((void**)&st.tf, sizeof(T) * n * NTF) ||
-      A((void**)&st.scratch, sizeof(T) * (size_t)n * G_TOTAL) || A((void**)&st.iscratch, sizeof(int) * (size_t)n * GI_TOTAL) ||
+      A((void**)&st.scratch, sizeof(T) * (size_t)s->nslots * G_TOTAL) || A((void**)&st.iscratch, sizeof(int) * (size_t)n * GI_TOTAL) ||
       A((void**)&st.t, sizeof(int) * n) || A((void**)&st.episode, sizeof(int) * n) || A((void**)&st.ep_goal, sizeof(int) * n) ||
       A((void**)&st.ep_return, sizeof(T) * n) || A((void**)&st.acc, sizeof(double) * 4 * n) ||
       A((void**)&st.overflow, sizeof(unsigned long long) * 2))
@@ -549,6 +558,7 @@ int launch_env(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode,
     configured = true;
   }
   int blocks = (st.n + WPB - 1) / WPB;
+  if (blocks > s->max_blocks) blocks = s->max_blocks;
   env_kernel<T><<<blocks, WPB * 32, smem, stream>>>(m, st, mode, action, mask, obs, reward, done, goal, debug);
   CK(cudaGetLastError());
   s->launches++;
@@ -566,6 +576,14 @@ int ensure_stage(adroit_sim* s, size_t n) {
 int run(adroit_sim* s, int mode, const float* action, const uint8_t* mask, float* obs, float* reward, uint8_t* done, uint8_t* goal,
         int debug, void* stream) {
   CK(cudaSetDevice(s->device));
+  if (debug && !(s->f64 ? (void*)s->sd.dbg_scratch : (void*)s->sf.dbg_scratch)) {   // per-env scratch only for introspection launches
+    void* p = nullptr;
+    size_t bytes = (s->f64 ? sizeof(double) : sizeof(float)) * (size_t)s->n * G_TOTAL;
+    CK(cudaMalloc(&p, bytes));
+    CK(cudaMemset(p, 0, bytes));
+    s->allocs.push_back(p);
+    if (s->f64) s->sd.dbg_scratch = (double*)p; else s->sf.dbg_scratch = (float*)p;
+  }
   if (s->f64) return launch_env<double>(s, s->md, s->sd, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
   return launch_env<float>(s, s->mf, s->sf, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
 }
@@ -624,6 +642,24 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
   if (cudaMalloc((void**)&s->arena.dev, s->arena.host.size()) != cudaSuccess) { delete s; FAIL("cudaMalloc(model) failed"); }
   s->allocs.push_back(s->arena.dev);
   CK(cudaMemcpy(s->arena.dev, s->arena.host.data(), s->arena.host.size(), cudaMemcpyHostToDevice));
+  {  // resident blocks of the step kernel: grid cap and number of scratch slots
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device_id));
+    int per_sm = 0;
+    size_t smem = s->f64 ? WPB * smem_per_warp<double>() : WPB * smem_per_warp<float>();
+    if (s->f64) {
+      CK(cudaFuncSetAttribute(env_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, env_kernel<double>, WPB * 32, smem));
+    } else {
+      CK(cudaFuncSetAttribute(env_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, env_kernel<float>, WPB * 32, smem));
+    }
+    if (per_sm < 1) { delete s; FAIL("step kernel does not fit on this device (shared memory %zu B per block)", smem); }
+    s->max_blocks = per_sm * prop.multiProcessorCount;
+    int need = (n_envs + WPB - 1) / WPB;
+    if (s->max_blocks > need) s->max_blocks = need;
+    s->nslots = s->max_blocks * WPB;
+  }
   int rc;
   if (s->f64) {
     patch_model(s->md, s->arena.dev);
@@ -745,9 +781,9 @@ int adroit_get_frames(adroit_sim* s, double* bx, double* bq, double* sx, void* s
   CK(cudaSetDevice(s->device));
   // frames are exported by a debug forward on the current state
   if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
-  if (bx && download_field(s, bx, STF(scratch), 3 * s->nbody, G_TOTAL, G_DBG_XPOS, st)) return 1;
-  if (bq && download_field(s, bq, STF(scratch), 4 * s->nbody, G_TOTAL, G_DBG_XQUAT, st)) return 1;
-  if (sx && download_field(s, sx, STF(scratch), 3 * s->nsite, G_TOTAL, G_SPOS, st)) return 1;
+  if (bx && download_field(s, bx, STF(dbg_scratch), 3 * s->nbody, G_TOTAL, G_DBG_XPOS, st)) return 1;
+  if (bq && download_field(s, bq, STF(dbg_scratch), 4 * s->nbody, G_TOTAL, G_DBG_XQUAT, st)) return 1;
+  if (sx && download_field(s, sx, STF(dbg_scratch), 3 * s->nsite, G_TOTAL, G_SPOS, st)) return 1;
   return 0;
 }
 
@@ -755,7 +791,7 @@ int adroit_get_solver(adroit_sim* s, double* qacc, int32_t* ncon, int32_t* nefc,
   cudaStream_t st = (cudaStream_t)stream;
   CK(cudaSetDevice(s->device));
   if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
-  if (qacc && download_field(s, qacc, STF(scratch), s->nv, G_TOTAL, G_DBG_QACC, st)) return 1;
+  if (qacc && download_field(s, qacc, STF(dbg_scratch), s->nv, G_TOTAL, G_DBG_QACC, st)) return 1;
   if (touch && download_field(s, touch, STF(tf), 1, NTF, 19, st)) return 1;
   if (ncon || nefc) {
     std::vector<int> gi((size_t)s->n * GI_TOTAL);
@@ -806,7 +842,8 @@ int adroit_overflow(adroit_sim* s, int64_t* out2_host, void* stream) {
 // debug: raw per-env scratch block (fp64 host buffer [n][count]) starting at T-offset `offset`; layout in csrc/model.cuh
 int adroit_debug_scratch(adroit_sim* s, int offset, int count, double* out_host, void* stream) {
   CK(cudaSetDevice(s->device));
-  return download_field(s, out_host, STF(scratch), count, G_TOTAL, offset, (cudaStream_t)stream);
+  if (!(s->f64 ? (void*)s->sd.dbg_scratch : (void*)s->sf.dbg_scratch)) FAIL("no introspection launch (set_state / get_frames / get_solver) has run yet");
+  return download_field(s, out_host, STF(dbg_scratch), count, G_TOTAL, offset, (cudaStream_t)stream);
 }
 int adroit_debug_iscratch(adroit_sim* s, int32_t* out_host, void* stream) {
   CK(cudaSetDevice(s->device));

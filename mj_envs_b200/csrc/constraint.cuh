@@ -577,7 +577,10 @@ template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
     T old = cost;
     cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
     iters = iter + 1;
-    if (scale * (old - cost) < m.tolerance) break;
+    // fp32: an improvement below the rounding noise of the cost itself (~1e-6 relative) cannot be measured; Newton's
+    // quadratic convergence makes the step after such an iteration a no-op, so stop there instead of burning a factorisation
+    T floor_ = sizeof(T) == 4 ? T(2e-6) * tabs(cost) : T(0);
+    if (scale * (old - cost) < m.tolerance || (old - cost) < floor_) break;
   }
   if (lane == 0) c.gi[GI_NITER] = iters;
 }

@@ -363,41 +363,54 @@ template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1,
   }
 }
 
-// in-place Cholesky A = L L^T (left-looking by columns, lane = row, vectorised dot products); dinv[j] = 1 / L[j][j]
+// in-place Cholesky A = L L^T; dinv[j] = 1 / L[j][j].  Leading min(n,32) block: left-looking by columns, lane = row,
+// vectorised dot products.  Rows 32..n-1 (n <= 36) are "bordered" on afterwards: each is one forward substitution
+// against the leading factor plus a few warp-wide dot products, instead of doubling every column step for 1-4 rows.
 template <typename T> __device__ __noinline__ void chol_dense(T* A, T* dinv, int n, int lane) {
-  const int i0 = lane, i1 = lane + 32;
-  T *r0 = A + rowoff(i0), *r1 = A + rowoff(i1 < n ? i1 : 0);
-  const bool two = n > 32;
-  for (int j = 0; j < n; j++) {
+  const int nb = n < 32 ? n : 32;
+  T* r0 = A + rowoff(lane);
+  for (int j = 0; j < nb; j++) {
     const T* rj = A + rowoff(j);
-    T s0 = 0, s1 = 0;
+    T s0 = 0;
     int k = 0;
     for (; k + 4 <= j; k += 4) {
       Vec4<T> b = ld4(rj + k), a = ld4(r0 + k);
       s0 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
-      if (two) {
-        Vec4<T> c = ld4(r1 + k);
-        s1 += c.v[0] * b.v[0] + c.v[1] * b.v[1] + c.v[2] * b.v[2] + c.v[3] * b.v[3];
-      }
     }
-    for (; k < j; k++) {
-      T b = rj[k];
-      s0 += r0[k] * b;
-      if (two) s1 += r1[k] * b;
-    }
-    s0 = r0[j] - s0;      // lanes with i0 < j read a neighbouring row: harmless, never stored
-    s1 = r1[j] - s1;
-    T d = __shfl_sync(0xffffffffu, j < 32 ? s0 : s1, j & 31);
+    for (; k < j; k++) s0 += r0[k] * rj[k];
+    s0 = r0[j] - s0;      // lanes with lane < j read a neighbouring row: harmless, never stored
+    T d = __shfl_sync(0xffffffffu, s0, j);
     d = d > tiny<T>() ? d : tiny<T>();
     T inv = rsqrt_t(d);
+    if (lane == j) { r0[j] = d * inv; dinv[j] = inv; }
+    else if (lane > j && lane < nb) r0[j] = s0 * inv;
     __syncwarp();
-    if (i0 == j) { r0[j] = d * inv; dinv[j] = inv; }
-    else if (i0 > j && i0 < n) r0[j] = s0 * inv;
-    if (two && i1 < n) {
-      if (i1 == j) { r1[j] = d * inv; dinv[j] = inv; }
-      else if (i1 > j) r1[j] = s1 * inv;
+  }
+  for (int r = 32; r < n; r++) {
+    T* rr = A + rowoff(r);
+    T x = rr[lane], dl = dinv[lane];
+    for (int k = 0; k < 32; k++) {          // L11 y = a
+      T yk = __shfl_sync(0xffffffffu, x * dl, k);
+      if (lane == k) x = yk;
+      if (lane > k) x -= r0[k] * yk;
     }
+    rr[lane] = x;
     __syncwarp();
+    for (int q = 32; q <= r; q++) {
+      const T* rq = A + rowoff(q);
+      T p = rr[lane] * rq[lane];
+      if (lane + 32 < q) p += rr[lane + 32] * rq[lane + 32];
+      p = warp_sum(p);
+      if (q < r) {
+        if (lane == 0) rr[q] = (rr[q] - p) * dinv[q];
+      } else {
+        T d = rr[r] - p;
+        d = d > tiny<T>() ? d : tiny<T>();
+        T inv = rsqrt_t(d);
+        if (lane == 0) { rr[r] = d * inv; dinv[r] = inv; }
+      }
+      __syncwarp();
+    }
   }
 }
 // x <- (L L^T)^-1 x  (x in shared memory)

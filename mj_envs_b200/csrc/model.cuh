@@ -121,7 +121,8 @@ template <typename T> struct DModel {
 // persistent per-env state + I/O pointers handed to the kernels
 template <typename T> struct DState {
   int n;
-  T *qpos, *qvel, *warm, *ctrl, *par, *tf, *scratch;   // [n][NVP] x4, [n][NPARP], [n][NTF], [n][G_TOTAL]
+  T *qpos, *qvel, *warm, *ctrl, *par, *tf;   // [n][NVP] x4, [n][NPARP], [n][NTF]
+  T *scratch, *dbg_scratch;                 // [resident warps][G_TOTAL]; [n][G_TOTAL], allocated by the first debug launch
   int* iscratch;                                // [n][GI_TOTAL]
   int *t, *episode, *ep_goal;                   // [n]
   T* ep_return;                                 // [n]

@@ -146,6 +146,8 @@ def test_env_state_round_trip_uses_reference_keys(task):
         env.step(torch.rand((8, env.nu)) * 2 - 1)
     sd = env.get_env_state()
     assert set(sd) == keys
+    if task != "relocate":
+        env.set_env_state(sd)   # = sim.forward(): after step() the reference's frames lag qpos by one substep (mujoco-py semantics)
     obs0 = env.get_obs().clone()
     env.reset()
     if task != "relocate":      # relocate's set_env_state rewrites body_pos from the world-frame obj_pos (relocate_v0.py:124-128)
