@@ -281,9 +281,9 @@ def main():
             r2 = measure(e2, n2, max(10, args.steps // 4), max(3, args.warmup // 4), False)
             line["also"][w] = {"value": r2["value"], "ms_per_step": r2["ms_per_step"], "overflow": r2["overflow"]}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sample = 256
-        v, dt, cores = cpu_reference_run(env_id, sample, 2, 1)
-        k = max(2, min(400, int(12.0 / max(dt / 2, 1e-6))))
+        sample = min(n_envs, 1024)
+        v, dt, cores = cpu_reference_run(env_id, sample, 4, 1)
+        k = max(2, min(20000, int(12.0 / max(dt / 4, 1e-6))))        # ~12 s of CPU work
         v, dt, cores = cpu_reference_run(env_id, sample, k, 1)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{env_id} x{sample} envs x {k} env.step() calls ({dt:.1f} s), fp64 oracle, OpenMP over envs; "
