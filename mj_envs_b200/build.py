@@ -19,13 +19,13 @@ def nvcc():
 def build(force=False, verbose=False, defines=(), out=None):
     """`defines`/`out` build an experiment variant (tools/ab.sh); the product library takes neither."""
     if out or defines:
-        cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
+        cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--expt-relaxed-constexpr", "-shared",
                "-Xcompiler", "-fPIC", "-o", out, SRC] + [f"-D{d}" for d in defines]
         subprocess.check_call(cmd)
         return out
     if not force and os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(d) for d in DEPS):
         return LIB
-    cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
+    cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--expt-relaxed-constexpr", "-shared",
            "-Xcompiler", "-fPIC", "-o", LIB, SRC]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")

@@ -1,8 +1,11 @@
 // adroit_b200.cu — kernels and the C ABI (include/adroit_b200.h) of the batched Adroit simulator for sm_100a.
 //
-// One warp advances one environment through a whole env.step(): action map -> frame_skip x mj_step ->
-// observation / reward / success -> (optional) auto-reset, in a single launch.  See DESIGN.md for the data layout and
-// the per-phase roofline; the reference call sites each entry point replaces are cited in include/adroit_b200.h.
+// One warp advances one environment.  An env.step() is a short sequence of PHASE KERNELS per physics substep
+// (smooth dynamics -> collision -> constraint solve -> noslip/Euler/task epilogue) that hand the per-env context to
+// each other through a context block in HBM/L2 (dynamics.cuh: Ctx, MAP).  Each phase kernel stages only the regions it
+// works on in shared memory, has its own register budget and occupancy, and is small enough for the instruction
+// cache; a step never synchronises with the host.  See DESIGN.md for the data layout and the per-phase roofline; the
+// reference call sites each entry point replaces are cited in include/adroit_b200.h.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -17,128 +20,67 @@ namespace adroit {
 
 enum { MODE_STEP = 0, MODE_RESET = 1, MODE_FORWARD = 2 };
 
-// ---------------------------------------------------------------- device pipeline
-// Block-wide phase alignment: the warps of a block run the same pipeline stage at the same time, so that the
-// instruction working set of an SM is one stage, not WPB different places of a ~500 KB kernel (ncu r1a: 62 % of the
-// stall samples were "no instruction").  Every warp of the block must reach every PHASE() -- inactive warps skip the
-// work but not the barrier.
-#ifndef ADROIT_PHASE_SYNC
-#define ADROIT_PHASE_SYNC 1
-#endif
-#if ADROIT_PHASE_SYNC
-#define PHASE() __syncthreads()
-#else
-#define PHASE() __syncwarp()
-#endif
+struct PArgs {
+  const float* action;        // smooth: action map (hammer_v0.py:55-59) when non-null
+  const uint8_t* mask;        // every phase: only envs with mask[env] != 0 (NULL = all)
+  float* obs;                 // finish: observation out (may be NULL)
+  float* reward;
+  uint8_t* done;
+  uint8_t* goal;
+  int reset;                  // smooth: reset_model prologue
+  int check;                  // smooth: mj_checkPos / mj_checkVel
+  int integrate;              // finish: mj_Euler
+  int epilogue;               // finish: reward / success / episode counters / auto-reset decision (last substep of a step)
+  int write_obs;              // finish: pack the observation
+  int debug;                  // export introspection copies (G_DBG_*)
+};
 
-template <typename T> __device__ __noinline__ void forward(Ctx<T>& c, const DState<T>& st, int debug, bool act) {
-  const DModel<T>& m = c.m;
-  const int nv = m.nv, lane = c.lane;
-  PHASE();
-  if (act) {
-    kinematics(c);
-    frames_and_inertia(c);
-    mass_matrix(c);
-    if (debug) {
-      for (int p = lane; p < nv * nv; p += 32) {   // exported as the plain packed lower triangle
-        int i = p / nv, j = p - i * nv;
-        if (j <= i) c.g[G_DBG_M + (i * (i + 1)) / 2 + j] = c.s[O_M + tri(i, j)];
-      }
-    }
-  }
-  PHASE();
-  if (act) collision(c, st.overflow);
-  PHASE();
-  const bool slip = m.noslip_iterations > 0;
-  if (act) {
-    rne_bias(c);
-    smooth_dynamics(c, slip);
-  }
-  PHASE();
-  if (act) make_constraint(c, st.overflow);
-  PHASE();
-  if (act) newton(c);
-  PHASE();
-  if (act) {
-    T *qacc = c.v(V_QACC), *qfc = c.v(V_QFC);
-    if (slip) {
-      noslip(c);
-      constraint_force(c);
-      T* u = c.v(V_T1);
-      symv(c.g + G_MINV, qfc, u, nv, lane);
-      __syncwarp();
-      for (int j = lane; j < nv; j += 32) qacc[j] = c.v(V_QAS)[j] + u[j];
-      __syncwarp();
-    }
-    T touch = touch_sensor(c);
-    cache_task_frames(c, touch);
-    if (lane == 0) { c.gi[GI_NCON] = c.ncon; c.gi[GI_NSIMPLE] = c.nsimple; }
-    if (debug) {
-      for (int j = lane; j < nv; j += 32) {
-        c.g[G_DBG_QFS + j] = c.v(V_QFS)[j];
-        c.g[G_DBG_QAS + j] = c.v(V_QAS)[j];
-        c.g[G_DBG_QACC + j] = qacc[j];
-        c.g[G_DBG_QFC + j] = qfc[j];
-      }
-      for (int i = lane; i < 3 * m.nbody; i += 32) c.g[G_DBG_XPOS + i] = c.s[O_XPOS + i];
-      for (int i = lane; i < 4 * m.nbody; i += 32) c.g[G_DBG_XQUAT + i] = c.s[O_XQUAT + i];
-      for (int i = lane; i < 6 * MAXCON; i += 32) c.g[G_DBG_EF + i] = c.s[O_EF + i];
-    }
-    __syncwarp();
-  }
-}
+#define VR(V, F) Reg{(V) * NVP, NVP, (F)}
+// ---- shared-memory maps of the phase kernels (everything not listed is addressed in the context block directly)
+struct MapSmooth {
+  static constexpr int NT = 17, NI = 1;
+  static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_CTRL, R_IN | R_OUT), VR(V_QFS, R_ZERO | R_OUT),
+                                 VR(V_QAS, R_ZERO | R_OUT), VR(V_T1, R_ZERO), VR(V_T2, R_ZERO), VR(V_DINV, R_ZERO),
+                                 Reg{O_PAR, NPARP, R_IN | R_OUT}, Reg{O_XPOS, NBP * 3, R_OUT}, Reg{O_XQUAT, NBP * 4, R_OUT},
+                                 Reg{O_XMAT, NBP * 9, R_OUT}, Reg{O_XANC, NVP * 3, R_OUT}, Reg{O_XAXIS, NVP * 3, R_OUT},
+                                 Reg{O_CRB, NBP * 10, 0}, Reg{O_M, NTRI, R_OUT}, Reg{O_H, NTRI, 0}};
+  static constexpr Reg RI[NI] = {Reg{I_SURV, 4, 0}};
+};
+struct MapCollide {
+  static constexpr int NT = 1, NI = 1;
+  static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}};
+  static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV, 0}};
+};
+struct MapSolve {
+  static constexpr int NT = 24, NI = 4;
+  static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_MA, R_ZERO),
+                                 VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_QFC, R_ZERO | R_OUT), VR(V_DINV, R_ZERO),
+                                 Reg{O_M, NTRI, R_IN}, Reg{O_H, NTRI, 0},
+                                 Reg{O_SD, MAXSIMPLE, R_OUT}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
+                                 Reg{O_AC, CROWS, 0}, Reg{O_AV, CROWS, 0}, Reg{O_CD, MAXCON, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
+                                 Reg{O_CAREFN, MAXCON, 0}, Reg{O_CBT, MAXCON * 3, R_OUT}, Reg{O_EF, MAXCON * 6, R_OUT}, Reg{O_W, MAXCON * 7, 0}};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MAXCON, R_IN}, Reg{I_CB1, MAXCON, R_IN}, Reg{I_CB2, MAXCON, R_IN}};
+};
+struct MapFinish {
+  static constexpr int NT = 20, NI = 2;
+  static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),
+                                 VR(V_QACC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_QFC, R_IN | R_OUT), VR(V_T1, R_ZERO),
+                                 VR(V_DINV, R_ZERO), Reg{O_H, NTRI, 0}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},
+                                 Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}, Reg{O_AV, CROWS, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
+                                 Reg{O_CBT, MAXCON * 3, R_IN}, Reg{O_EF, MAXCON * 6, R_IN | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON, R_IN}};
+};
+#undef VR
 
 template <typename T> DI bool warp_bad(const T* x, int n, int lane) {
   bool bad = false;
   for (int j = lane; j < n; j += 32) bad |= !(tabs(x[j]) < T(1e10));
   return __any_sync(0xffffffffu, bad);
 }
-template <typename T> DI void zero_state(Ctx<T>& c) {
-  for (int j = c.lane; j < NVP; j += 32) { c.v(V_QPOS)[j] = 0; c.v(V_QVEL)[j] = 0; c.v(V_WARM)[j] = 0; }
-  __syncwarp();
-}
-
-// mj_step: forward + semi-implicit Euler with implicit joint damping
-template <typename T> __device__ void substep(Ctx<T>& c, const DState<T>& st, int debug, bool act) {
-  const DModel<T>& m = c.m;
-  const int nv = m.nv, lane = c.lane;
-  if (act && (warp_bad(c.v(V_QPOS), nv, lane) || warp_bad(c.v(V_QVEL), nv, lane))) zero_state(c);  // mj_checkPos / mj_checkVel
-  forward(c, st, debug, act);
-  bool bad = act && warp_bad(c.v(V_QACC), nv, lane);  // mj_checkAcc
-#if ADROIT_PHASE_SYNC
-  bool any_bad = __syncthreads_or(bad);
-#else
-  bool any_bad = bad;
-#endif
-  if (any_bad) {
-    if (bad) zero_state(c);
-    forward(c, st, debug, bad);
-  }
-  PHASE();
-  if (!act) return;
-  T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL), *warm = c.v(V_WARM), *qacc = c.v(V_QACC), *x = c.v(V_T1);
-  const T h = m.timestep;
-  if (m.any_damping) {
-    T *H = c.s + O_H, *M = c.s + O_M;
-    for (int p = lane; p < NTRI; p += 32) H[p] = M[p];
-    __syncwarp();
-    for (int j = lane; j < nv; j += 32) {
-      H[tri(j, j)] += h * m.dof_damping[j];
-      x[j] = c.v(V_QFS)[j] + c.v(V_QFC)[j];
-    }
-    __syncwarp();
-    ltdl_factor(m, H, c.v(V_DINV), lane);    // M + h*diag(damping) keeps the tree sparsity of M
-    ltdl_solve(H, c.v(V_DINV), x, nv, lane);
-  } else {
-    for (int j = lane; j < nv; j += 32) x[j] = qacc[j];
-    __syncwarp();
-  }
-  for (int j = lane; j < nv; j += 32) {
-    T v = qvel[j] + h * x[j];
-    qvel[j] = v;
-    qpos[j] += h * v;
-    warm[j] = qacc[j];
-  }
+template <class C> DI void zero_state(C& c) {
+  using T = typename C::real;
+  T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *warm = c.template V<V_WARM>();
+  for (int j = c.lane; j < NVP; j += 32) { qpos[j] = 0; qvel[j] = 0; warm[j] = 0; }
   __syncwarp();
 }
 
@@ -152,117 +94,191 @@ template <typename T> __device__ void episode_finish(const DModel<T>& m, const D
   a[3] += 1;
 }
 
-// reset_model (hammer_v0.py:106-132, door_v0.py:103-119, pen_v0.py:115-132, relocate_v0.py:85-103) + mj_forward
-template <typename T> __device__ void reset_env(Ctx<T>& c, const DState<T>& st, int env, int debug, bool act) {
-  const DModel<T>& m = c.m;
-  if (act && c.lane == 0) {
-    episode_finish(m, st, env);
-    T par[NPARP];
-    draw_params(m, st.seed, (unsigned long long)(st.env_off + env), (unsigned)st.episode[env], par);
-    for (int i = 0; i < m.npar; i++) c.s[O_PAR + i] = par[i];
-    st.episode[env] += 1;
-    st.t[env] = 0;
-    st.ep_return[env] = 0;
-    st.ep_goal[env] = 0;
-  }
-  if (act) {
-    for (int j = c.lane; j < NVP; j += 32) c.v(V_CTRL)[j] = 0;
+// common prologue of a phase kernel: env of this warp, context pointers, staging
+#define PHASE_PROLOGUE(MAP)                                                                                             \
+  extern __shared__ __align__(16) unsigned char smem_raw[];                                                              \
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;                                                            \
+  const int env = blockIdx.x * WPB + warp;                                                                               \
+  if (env >= st.n) return;                        /* no block-wide barrier anywhere in a phase kernel */                 \
+  if (a.mask && !a.mask[env]) return;                                                                                    \
+  T* sm_ = reinterpret_cast<T*>(smem_raw) + (size_t)warp * map_st<MAP>();                                                \
+  int* smi_ = reinterpret_cast<int*>(smem_raw + (size_t)WPB * map_st<MAP>() * sizeof(T)) + warp * map_si<MAP>();         \
+  Ctx<T, MAP> c(m, sm_, smi_, st.ctx + (size_t)env * CTX_T, st.ctxi + (size_t)env * CTX_I, lane);                        \
+  stage_in(c);                                                                                                           \
+  __syncwarp();
+
+// ---------------------------------------------------------------- phase 1: smooth dynamics
+// [reset_model prologue] [action map] [mj_checkPos/Vel] kinematics, frames, CRB, RNE, actuation, L^T D L, qacc_smooth, M^-1
+template <typename T>
+__global__ void __launch_bounds__(WPB * 32) smooth_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+                                                           const __grid_constant__ PArgs a) {
+  PHASE_PROLOGUE(MapSmooth)
+  const int nv = m.nv;
+  if (a.reset) {
+    // reset_model (hammer_v0.py:106-132, door_v0.py:103-119, pen_v0.py:115-132, relocate_v0.py:85-103)
+    if (lane == 0) {
+      episode_finish(m, st, env);
+      T par[NPARP];
+      draw_params(m, st.seed, (unsigned long long)(st.env_off + env), (unsigned)st.episode[env], par);
+      T* P = c.template S<O_PAR>();
+      for (int i = 0; i < m.npar; i++) P[i] = par[i];
+      st.episode[env] += 1;
+      st.t[env] = 0;
+      st.ep_return[env] = 0;
+      st.ep_goal[env] = 0;
+    }
+    T* ctrl = c.template V<V_CTRL>();
+    for (int j = lane; j < NVP; j += 32) ctrl[j] = 0;
     zero_state(c);
   }
-  forward(c, st, debug, act);
+  if (a.action) {   // action map: hammer_v0.py:55-59 (act_mid / act_rng :49-50)
+    T* ctrl = c.template V<V_CTRL>();
+    for (int u = lane; u < m.nu; u += 32) {
+      T x = tclamp((T)a.action[(size_t)env * m.nu + u], T(-1), T(1));
+      T lo = m.act_ctrlrange[2 * u], hi = m.act_ctrlrange[2 * u + 1];
+      ctrl[u] = T(0.5) * (lo + hi) + x * T(0.5) * (hi - lo);
+    }
+    __syncwarp();
+  }
+  if (a.check && (warp_bad(c.template V<V_QPOS>(), nv, lane) || warp_bad(c.template V<V_QVEL>(), nv, lane))) zero_state(c);  // mj_checkPos / mj_checkVel
+  kinematics(c);
+  frames_and_inertia(c);
+  mass_matrix(c);
+  if (a.debug) {
+    const T* M = c.template S<O_M>();
+    T* D = c.template G<G_DBG_M>();
+    for (int p = lane; p < nv * nv; p += 32) {   // exported as the plain packed lower triangle
+      int i = p / nv, j = p - i * nv;
+      if (j <= i) D[(i * (i + 1)) / 2 + j] = M[tri(i, j)];
+    }
+  }
+  rne_bias(c);
+  smooth_dynamics(c, m.noslip_iterations > 0);
+  __syncwarp();
+  stage_out(c);
 }
 
+// ---------------------------------------------------------------- phase 2: collision
 template <typename T>
-__global__ void __launch_bounds__(WPB * 32) env_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, int mode, const float* __restrict__ action,
-                                                        const uint8_t* __restrict__ mask, float* obs, float* reward, uint8_t* done,
-                                                        uint8_t* goal, int debug) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // persistent blocks: the grid is sized to what is resident at once and walks the env tiles, so the per-warp global
-  // scratch (G_TOTAL words) is one slot per RESIDENT warp -- it stays in L2 however many envs the handle owns
-  const int ntiles = (st.n + WPB - 1) / WPB;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-  const int env_raw = tile * WPB + warp;
-  const int env = env_raw < st.n ? env_raw : st.n - 1;   // out-of-range warps idle on a valid index (they only take part in barriers)
-  T* s = reinterpret_cast<T*>(smem_raw) + (size_t)warp * SM_T;
-  int* si = reinterpret_cast<int*>(smem_raw + (size_t)WPB * SM_T * sizeof(T)) + warp * SM_I;
-  T* gscratch = debug ? st.dbg_scratch + (size_t)env * G_TOTAL : st.scratch + (size_t)(blockIdx.x * WPB + warp) * G_TOTAL;
-  Ctx<T> c(m, s, si, gscratch, st.iscratch + (size_t)env * GI_TOTAL, lane);
-  const bool act = env_raw < st.n && !(mode == MODE_RESET && mask && !mask[env]);
+__global__ void __launch_bounds__(WPB * 32) collide_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+                                                            const __grid_constant__ PArgs a) {
+  PHASE_PROLOGUE(MapCollide)
+  collision(c, st.overflow);
+  if (lane == 0) c.gi[GI_NCON] = c.ncon;
+}
 
-  for (int j = lane; j < V_COUNT * NVP; j += 32) s[j] = 0;   // tails [nv, NVP) of every work vector stay zero (vector loads read them)
+// ---------------------------------------------------------------- phase 3: constraint rows + Newton
+template <typename T>
+__global__ void __launch_bounds__(WPB * 32) solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+                                                          const __grid_constant__ PArgs a) {
+  PHASE_PROLOGUE(MapSolve)
+  c.ncon = c.gi[GI_NCON];
+  make_constraint(c, st.overflow);
+  newton(c);
+  if (lane == 0) c.gi[GI_NSIMPLE] = c.nsimple;
   __syncwarp();
-  // stage the persistent state
-  if (act) {
-    for (int j = lane; j < NVP; j += 32) {
-      c.v(V_QPOS)[j] = st.qpos[(size_t)env * NVP + j];
-      c.v(V_QVEL)[j] = st.qvel[(size_t)env * NVP + j];
-      c.v(V_WARM)[j] = st.warm[(size_t)env * NVP + j];
-      c.v(V_CTRL)[j] = st.ctrl[(size_t)env * NVP + j];   // data.ctrl persists between calls (MjSim semantics)
+  stage_out(c);
+}
+
+// ---------------------------------------------------------------- phase 4: noslip, sensors, Euler, task epilogue
+template <typename T>
+__global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+                                                           const __grid_constant__ PArgs a) {
+  PHASE_PROLOGUE(MapFinish)
+  const int nv = m.nv;
+  c.ncon = c.gi[GI_NCON];
+  c.nsimple = c.gi[GI_NSIMPLE];
+  T *qacc = c.template V<V_QACC>(), *qfc = c.template V<V_QFC>();
+  if (m.noslip_iterations > 0) {
+    noslip(c);
+    constraint_force(c);
+    T* u = c.template V<V_T1>();
+    symv(c.template G<G_MINV>(), qfc, u, nv, lane);
+    __syncwarp();
+    const T* qas = c.template V<V_QAS>();
+    for (int j = lane; j < nv; j += 32) qacc[j] = qas[j] + u[j];
+    __syncwarp();
+  }
+  T touch = touch_sensor(c);
+  cache_task_frames(c, touch);
+  if (a.debug) {
+    const T *qfs = c.template V<V_QFS>(), *qas = c.template V<V_QAS>();
+    for (int j = lane; j < nv; j += 32) {
+      c.template G<G_DBG_QFS>()[j] = qfs[j];
+      c.template G<G_DBG_QAS>()[j] = qas[j];
+      c.template G<G_DBG_QACC>()[j] = qacc[j];
+      c.template G<G_DBG_QFC>()[j] = qfc[j];
     }
-    if (lane < NPARP) s[O_PAR + lane] = st.par[(size_t)env * NPARP + lane];
-    if (lane < NTF) s[O_TF + lane] = st.tf[(size_t)env * NTF + lane];
+    for (int i = lane; i < 3 * m.nbody; i += 32) c.template G<G_DBG_XPOS>()[i] = c.template S<O_XPOS>()[i];
+    for (int i = lane; i < 4 * m.nbody; i += 32) c.template G<G_DBG_XQUAT>()[i] = c.template S<O_XQUAT>()[i];
+    for (int i = lane; i < 6 * MAXCON; i += 32) c.template G<G_DBG_EF>()[i] = c.template S<O_EF>()[i];
   }
   __syncwarp();
-
-  if (mode == MODE_RESET) {
-    reset_env(c, st, env, debug, act);
-  } else if (mode == MODE_FORWARD) {
-    forward(c, st, debug, act);
-  } else {
-    // action map: hammer_v0.py:55-59 (act_mid / act_rng :49-50)
-    if (act)
-      for (int u = lane; u < m.nu; u += 32) {
-        T a = tclamp((T)action[(size_t)env * m.nu + u], T(-1), T(1));
-        T lo = m.act_ctrlrange[2 * u], hi = m.act_ctrlrange[2 * u + 1];
-        c.v(V_CTRL)[u] = T(0.5) * (lo + hi) + a * T(0.5) * (hi - lo);
+  T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *warm = c.template V<V_WARM>();
+  if (a.integrate) {
+    // mj_checkAcc: a non-finite acceleration resets the env's data (MuJoCo then re-runs mj_forward on the reset
+    // state and integrates it; here the env simply restarts from the reset state on the next substep)
+    if (warp_bad(qacc, nv, lane)) {
+      zero_state(c);
+    } else {
+      // mj_Euler: semi-implicit with implicit joint damping, (M + h*diag(damping)) keeps the tree sparsity of M
+      T* x = c.template V<V_T1>();
+      const T h = m.timestep;
+      if (m.any_damping) {
+        T* H = c.template S<O_H>();
+        const T* M = c.template S<O_M>();
+        const T *qfs = c.template V<V_QFS>();
+        for (int p = lane; p < NTRI; p += 32) H[p] = M[p];
+        __syncwarp();
+        for (int j = lane; j < nv; j += 32) {
+          H[tri(j, j)] += h * m.dof_damping[j];
+          x[j] = qfs[j] + qfc[j];
+        }
+        __syncwarp();
+        ltdl_factor(m, H, c.template V<V_DINV>(), lane);
+        ltdl_solve(H, c.template V<V_DINV>(), x, nv, lane);
+      } else {
+        for (int j = lane; j < nv; j += 32) x[j] = qacc[j];
+        __syncwarp();
       }
-    __syncwarp();
-    for (int k = 0; k < m.frame_skip; k++) substep(c, st, debug, act);  // do_simulation
-    bool reset_now = false;
-    if (act) {
-      T r;
-      int g, dn;
-      task_reward(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, lane, r, g, dn);
-      int tnew = st.t[env] + 1;
-      bool trunc = (st.flags & ADROIT_AUTO_RESET) && tnew >= m.horizon;
-      reset_now = trunc || ((st.flags & ADROIT_AUTO_RESET) && (st.flags & ADROIT_RESET_ON_DONE) && dn);
-      if (lane == 0) {
-        st.t[env] = tnew;
-        st.ep_return[env] += r;
-        st.ep_goal[env] += g;
-        if (reward) reward[env] = (float)r;
-        if (goal) goal[env] = (uint8_t)g;
-        if (done) done[env] = (uint8_t)(dn || trunc);
+      for (int j = lane; j < nv; j += 32) {
+        T v = qvel[j] + h * x[j];
+        qvel[j] = v;
+        qpos[j] += h * v;
+        warm[j] = qacc[j];
       }
       __syncwarp();
     }
-#if ADROIT_PHASE_SYNC
-    bool any_reset = __syncthreads_or(reset_now);
-#else
-    bool any_reset = reset_now;
-#endif
-    if (any_reset) reset_env(c, st, env, debug, reset_now);
   }
-  if (act) {
-    if (obs) write_obs(m, c.v(V_QPOS), c.v(V_QVEL), s + O_TF, obs + (size_t)env * m.obs_dim, lane);
-    for (int j = lane; j < NVP; j += 32) {
-      st.qpos[(size_t)env * NVP + j] = c.v(V_QPOS)[j];
-      st.qvel[(size_t)env * NVP + j] = c.v(V_QVEL)[j];
-      st.warm[(size_t)env * NVP + j] = c.v(V_WARM)[j];
-      st.ctrl[(size_t)env * NVP + j] = c.v(V_CTRL)[j];
+  bool reset_now = false;
+  if (a.epilogue) {
+    T r;
+    int g, dn;
+    task_reward(m, qpos, qvel, c.template S<O_TF>(), lane, r, g, dn);
+    int tnew = st.t[env] + 1;
+    bool trunc = (st.flags & ADROIT_AUTO_RESET) && tnew >= m.horizon;
+    reset_now = trunc || ((st.flags & ADROIT_AUTO_RESET) && (st.flags & ADROIT_RESET_ON_DONE) && dn);
+    if (lane == 0) {
+      st.t[env] = tnew;
+      st.ep_return[env] += r;
+      st.ep_goal[env] += g;
+      st.reset_flag[env] = reset_now ? 1 : 0;
+      if (a.reward) a.reward[env] = (float)r;
+      if (a.goal) a.goal[env] = (uint8_t)g;
+      if (a.done) a.done[env] = (uint8_t)(dn || trunc);
     }
-    if (lane < NPARP) st.par[(size_t)env * NPARP + lane] = s[O_PAR + lane];
-    if (lane < NTF) st.tf[(size_t)env * NTF + lane] = s[O_TF + lane];
+    __syncwarp();
   }
+  if (a.write_obs && a.obs && !reset_now) write_obs(m, qpos, qvel, c.template S<O_TF>(), a.obs + (size_t)env * m.obs_dim, lane);
   __syncwarp();
-  }  // tile loop
+  stage_out(c);
 }
 
 template <typename T> __global__ void obs_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, float* obs) {
   int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (env >= st.n) return;
-  write_obs(m, st.qpos + (size_t)env * NVP, st.qvel + (size_t)env * NVP, st.tf + (size_t)env * NTF, obs + (size_t)env * m.obs_dim, lane);
+  const T* b = st.ctx + (size_t)env * CTX_T;
+  write_obs(m, b + V_QPOS * NVP, b + V_QVEL * NVP, b + O_TF, obs + (size_t)env * m.obs_dim, lane);
 }
 
 // [n][w] <-> padded [n][stride] conversions between the fp64 host staging buffer and the typed device arrays
@@ -303,6 +319,7 @@ __global__ void reduce_kernel(const double* acc, const int* t, const int* ep_goa
 }
 
 }  // namespace adroit
+
 
 // ================================================================ host side
 using namespace adroit;
@@ -384,7 +401,6 @@ struct adroit_sim {
   uint8_t *d_done = nullptr, *d_goal = nullptr;
   double* d_out4 = nullptr;
   int64_t launches = 0;
-  int max_blocks = 0, nslots = 0;   // resident blocks of env_kernel on this device / scratch slots (= max_blocks * WPB)
 };
 
 namespace {
@@ -536,32 +552,69 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
     return 0;
   };
   st.n = n;
-  if (A((void**)&st.qpos, sizeof(T) * n * NVP) || A((void**)&st.qvel, sizeof(T) * n * NVP) || A((void**)&st.warm, sizeof(T) * n * NVP) ||
-      A((void**)&st.ctrl, sizeof(T) * n * NVP) ||
-      A((void**)&st.par, sizeof(T) * n * NPARP) || A((void**)&st.tf, sizeof(T) * n * NTF) ||
-      A((void**)&st.scratch, sizeof(T) * (size_t)s->nslots * G_TOTAL) || A((void**)&st.iscratch, sizeof(int) * (size_t)n * GI_TOTAL) ||
+  if (A((void**)&st.ctx, sizeof(T) * (size_t)n * CTX_T) || A((void**)&st.ctxi, sizeof(int) * (size_t)n * CTX_I) ||
       A((void**)&st.t, sizeof(int) * n) || A((void**)&st.episode, sizeof(int) * n) || A((void**)&st.ep_goal, sizeof(int) * n) ||
-      A((void**)&st.ep_return, sizeof(T) * n) || A((void**)&st.acc, sizeof(double) * 4 * n) ||
+      A((void**)&st.ep_return, sizeof(T) * n) || A((void**)&st.acc, sizeof(double) * 4 * n) || A((void**)&st.reset_flag, n) ||
       A((void**)&st.overflow, sizeof(unsigned long long) * 2))
     return 1;
   return 0;
 }
 
-template <typename T>
-int launch_env(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, const float* action, const uint8_t* mask, float* obs,
-               float* reward, uint8_t* done, uint8_t* goal, int debug, cudaStream_t stream) {
-  size_t smem = WPB * smem_per_warp<T>();
-  static thread_local bool configured_f = false, configured_d = false;
-  bool& configured = sizeof(T) == 4 ? configured_f : configured_d;
-  if (!configured) {
-    CK(cudaFuncSetAttribute(env_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
-  }
+template <typename T, class MAP, typename K>
+int launch_phase(adroit_sim* s, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {
+  size_t smem = WPB * map_bytes<T, MAP>();
   int blocks = (st.n + WPB - 1) / WPB;
-  if (blocks > s->max_blocks) blocks = s->max_blocks;
-  env_kernel<T><<<blocks, WPB * 32, smem, stream>>>(m, st, mode, action, mask, obs, reward, done, goal, debug);
+  kernel<<<blocks, WPB * 32, smem, stream>>>(m, st, a);
   CK(cudaGetLastError());
   s->launches++;
+  return 0;
+}
+
+template <typename T> int configure_kernels() {
+  CK(cudaFuncSetAttribute(smooth_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSmooth>())));
+  CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapCollide>())));
+  CK(cudaFuncSetAttribute(solve_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSolve>())));
+  CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapFinish>())));
+  return 0;
+}
+
+// one mj_forward (+ optional Euler / task epilogue) over the envs selected by a.mask: the four phase kernels in order
+template <typename T> int forward_pass(adroit_sim* s, const DModel<T>& m, const DState<T>& st, PArgs a, cudaStream_t stream) {
+  if (launch_phase<T, MapSmooth>(s, smooth_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapCollide>(s, collide_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapSolve>(s, solve_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapFinish>(s, finish_kernel<T>, m, st, a, stream)) return 1;
+  return 0;
+}
+
+template <typename T>
+int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, const float* action, const uint8_t* mask, float* obs, float* reward,
+          uint8_t* done, uint8_t* goal, int debug, cudaStream_t stream) {
+  PArgs a;
+  memset(&a, 0, sizeof a);
+  a.debug = debug;
+  if (mode == MODE_FORWARD) {            // sim.forward()
+    a.mask = mask;
+    return forward_pass(s, m, st, a, stream);
+  }
+  if (mode == MODE_RESET) {              // env.reset(): reset_model + mj_forward + get_obs
+    a.mask = mask; a.reset = 1; a.obs = obs; a.write_obs = obs != nullptr;
+    return forward_pass(s, m, st, a, stream);
+  }
+  // env.step(): action map, frame_skip x mj_step, task epilogue; then reset_model for the envs the epilogue flagged
+  for (int k = 0; k < m.frame_skip; k++) {
+    PArgs b = a;
+    b.action = k == 0 ? action : nullptr;
+    b.check = 1;
+    b.integrate = 1;
+    if (k == m.frame_skip - 1) { b.epilogue = 1; b.write_obs = obs != nullptr; b.obs = obs; b.reward = reward; b.done = done; b.goal = goal; }
+    if (forward_pass(s, m, st, b, stream)) return 1;
+  }
+  if (st.flags & ADROIT_AUTO_RESET) {
+    PArgs r = a;
+    r.mask = st.reset_flag; r.reset = 1; r.obs = obs; r.write_obs = obs != nullptr;
+    if (forward_pass(s, m, st, r, stream)) return 1;
+  }
   return 0;
 }
 
@@ -576,26 +629,18 @@ int ensure_stage(adroit_sim* s, size_t n) {
 int run(adroit_sim* s, int mode, const float* action, const uint8_t* mask, float* obs, float* reward, uint8_t* done, uint8_t* goal,
         int debug, void* stream) {
   CK(cudaSetDevice(s->device));
-  if (debug && !(s->f64 ? (void*)s->sd.dbg_scratch : (void*)s->sf.dbg_scratch)) {   // per-env scratch only for introspection launches
-    void* p = nullptr;
-    size_t bytes = (s->f64 ? sizeof(double) : sizeof(float)) * (size_t)s->n * G_TOTAL;
-    CK(cudaMalloc(&p, bytes));
-    CK(cudaMemset(p, 0, bytes));
-    s->allocs.push_back(p);
-    if (s->f64) s->sd.dbg_scratch = (double*)p; else s->sf.dbg_scratch = (float*)p;
-  }
-  if (s->f64) return launch_env<double>(s, s->md, s->sd, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
-  return launch_env<float>(s, s->mf, s->sf, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
+  if (s->f64) return run_t<double>(s, s->md, s->sd, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
+  return run_t<float>(s, s->mf, s->sf, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
 }
 
 // host fp64 [n][w]  ->  device typed [n][stride]
-int upload_field(adroit_sim* s, const double* host, void* dev, int w, int stride, cudaStream_t st) {
+int upload_field(adroit_sim* s, const double* host, void* dev, int w, int stride, int offset, cudaStream_t st) {
   size_t cnt = (size_t)s->n * w;
   if (ensure_stage(s, cnt)) return 1;
   CK(cudaMemcpyAsync(s->stage, host, cnt * sizeof(double), cudaMemcpyHostToDevice, st));
   int thr = 256, blk = (int)((cnt + thr - 1) / thr);
-  if (s->f64) pack_kernel<double><<<blk, thr, 0, st>>>((double*)dev, s->stage, s->n, w, stride);
-  else pack_kernel<float><<<blk, thr, 0, st>>>((float*)dev, s->stage, s->n, w, stride);
+  if (s->f64) pack_kernel<double><<<blk, thr, 0, st>>>((double*)dev + offset, s->stage, s->n, w, stride);
+  else pack_kernel<float><<<blk, thr, 0, st>>>((float*)dev + offset, s->stage, s->n, w, stride);
   CK(cudaGetLastError());
   s->launches++;
   CK(cudaStreamSynchronize(st));
@@ -616,7 +661,7 @@ int download_field(adroit_sim* s, double* host, const void* dev, int w, int stri
 
 }  // namespace
 
-#define STF(field) (s->f64 ? (void*)s->sd.field : (void*)s->sf.field)
+#define CTXP (s->f64 ? (void*)s->sd.ctx : (void*)s->sf.ctx)
 
 extern "C" {
 
@@ -642,24 +687,7 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
   if (cudaMalloc((void**)&s->arena.dev, s->arena.host.size()) != cudaSuccess) { delete s; FAIL("cudaMalloc(model) failed"); }
   s->allocs.push_back(s->arena.dev);
   CK(cudaMemcpy(s->arena.dev, s->arena.host.data(), s->arena.host.size(), cudaMemcpyHostToDevice));
-  {  // resident blocks of the step kernel: grid cap and number of scratch slots
-    cudaDeviceProp prop;
-    CK(cudaGetDeviceProperties(&prop, device_id));
-    int per_sm = 0;
-    size_t smem = s->f64 ? WPB * smem_per_warp<double>() : WPB * smem_per_warp<float>();
-    if (s->f64) {
-      CK(cudaFuncSetAttribute(env_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, env_kernel<double>, WPB * 32, smem));
-    } else {
-      CK(cudaFuncSetAttribute(env_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, env_kernel<float>, WPB * 32, smem));
-    }
-    if (per_sm < 1) { delete s; FAIL("step kernel does not fit on this device (shared memory %zu B per block)", smem); }
-    s->max_blocks = per_sm * prop.multiProcessorCount;
-    int need = (n_envs + WPB - 1) / WPB;
-    if (s->max_blocks > need) s->max_blocks = need;
-    s->nslots = s->max_blocks * WPB;
-  }
+  if (s->f64 ? configure_kernels<double>() : configure_kernels<float>()) { delete s; return 1; }
   int rc;
   if (s->f64) {
     patch_model(s->md, s->arena.dev);
@@ -679,7 +707,7 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
   std::vector<double> par((size_t)n_envs * s->npar);
   for (int e = 0; e < n_envs; e++)
     for (int i = 0; i < s->npar; i++) par[(size_t)e * s->npar + i] = s->f64 ? s->md.par0[i] : (double)s->mf.par0[i];
-  if (upload_field(s, par.data(), STF(par), s->npar, NPARP, 0)) { adroit_destroy(s); return 1; }
+  if (upload_field(s, par.data(), CTXP, s->npar, CTX_T, O_PAR, 0)) { adroit_destroy(s); return 1; }
   if (cudaMalloc((void**)&s->d_out4, 4 * sizeof(double)) != cudaSuccess) { adroit_destroy(s); FAIL("cudaMalloc failed"); }
   s->allocs.push_back(s->d_out4);
   if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr)) { adroit_destroy(s); return 1; }
@@ -750,18 +778,18 @@ int adroit_get_obs(adroit_sim* s, float* obs_dev, void* stream) {
 int adroit_get_state(adroit_sim* s, double* qpos, double* qvel, double* par, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   CK(cudaSetDevice(s->device));
-  if (qpos && download_field(s, qpos, STF(qpos), s->nv, NVP, 0, st)) return 1;
-  if (qvel && download_field(s, qvel, STF(qvel), s->nv, NVP, 0, st)) return 1;
-  if (par && download_field(s, par, STF(par), s->npar, NPARP, 0, st)) return 1;
+  if (qpos && download_field(s, qpos, CTXP, s->nv, CTX_T, V_QPOS * NVP, st)) return 1;
+  if (qvel && download_field(s, qvel, CTXP, s->nv, CTX_T, V_QVEL * NVP, st)) return 1;
+  if (par && download_field(s, par, CTXP, s->npar, CTX_T, O_PAR, st)) return 1;
   return 0;
 }
 
 int adroit_set_state(adroit_sim* s, const double* qpos, const double* qvel, const double* par, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   CK(cudaSetDevice(s->device));
-  if (qpos && upload_field(s, qpos, STF(qpos), s->nv, NVP, st)) return 1;
-  if (qvel && upload_field(s, qvel, STF(qvel), s->nv, NVP, st)) return 1;
-  if (par && upload_field(s, par, STF(par), s->npar, NPARP, st)) return 1;
+  if (qpos && upload_field(s, qpos, CTXP, s->nv, CTX_T, V_QPOS * NVP, st)) return 1;
+  if (qvel && upload_field(s, qvel, CTXP, s->nv, CTX_T, V_QVEL * NVP, st)) return 1;
+  if (par && upload_field(s, par, CTXP, s->npar, CTX_T, O_PAR, st)) return 1;
   if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
   CK(cudaStreamSynchronize(st));
   return 0;
@@ -769,11 +797,11 @@ int adroit_set_state(adroit_sim* s, const double* qpos, const double* qvel, cons
 
 int adroit_get_warmstart(adroit_sim* s, double* w, void* stream) {
   CK(cudaSetDevice(s->device));
-  return download_field(s, w, STF(warm), s->nv, NVP, 0, (cudaStream_t)stream);
+  return download_field(s, w, CTXP, s->nv, CTX_T, V_WARM * NVP, (cudaStream_t)stream);
 }
 int adroit_set_warmstart(adroit_sim* s, const double* w, void* stream) {
   CK(cudaSetDevice(s->device));
-  return upload_field(s, w, STF(warm), s->nv, NVP, (cudaStream_t)stream);
+  return upload_field(s, w, CTXP, s->nv, CTX_T, V_WARM * NVP, (cudaStream_t)stream);
 }
 
 int adroit_get_frames(adroit_sim* s, double* bx, double* bq, double* sx, void* stream) {
@@ -781,9 +809,9 @@ int adroit_get_frames(adroit_sim* s, double* bx, double* bq, double* sx, void* s
   CK(cudaSetDevice(s->device));
   // frames are exported by a debug forward on the current state
   if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
-  if (bx && download_field(s, bx, STF(dbg_scratch), 3 * s->nbody, G_TOTAL, G_DBG_XPOS, st)) return 1;
-  if (bq && download_field(s, bq, STF(dbg_scratch), 4 * s->nbody, G_TOTAL, G_DBG_XQUAT, st)) return 1;
-  if (sx && download_field(s, sx, STF(dbg_scratch), 3 * s->nsite, G_TOTAL, G_SPOS, st)) return 1;
+  if (bx && download_field(s, bx, CTXP, 3 * s->nbody, CTX_T, O_XPOS, st)) return 1;
+  if (bq && download_field(s, bq, CTXP, 4 * s->nbody, CTX_T, O_XQUAT, st)) return 1;
+  if (sx && download_field(s, sx, CTXP, 3 * s->nsite, CTX_T, SM_T + G_SPOS, st)) return 1;
   return 0;
 }
 
@@ -791,14 +819,14 @@ int adroit_get_solver(adroit_sim* s, double* qacc, int32_t* ncon, int32_t* nefc,
   cudaStream_t st = (cudaStream_t)stream;
   CK(cudaSetDevice(s->device));
   if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
-  if (qacc && download_field(s, qacc, STF(dbg_scratch), s->nv, G_TOTAL, G_DBG_QACC, st)) return 1;
-  if (touch && download_field(s, touch, STF(tf), 1, NTF, 19, st)) return 1;
+  if (qacc && download_field(s, qacc, CTXP, s->nv, CTX_T, V_QACC * NVP, st)) return 1;
+  if (touch && download_field(s, touch, CTXP, 1, CTX_T, O_TF + 19, st)) return 1;
   if (ncon || nefc) {
-    std::vector<int> gi((size_t)s->n * GI_TOTAL);
-    CK(cudaMemcpyAsync(gi.data(), s->f64 ? s->sd.iscratch : s->sf.iscratch, gi.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+    std::vector<int> gi((size_t)s->n * CTX_I);
+    CK(cudaMemcpyAsync(gi.data(), s->f64 ? s->sd.ctxi : s->sf.ctxi, gi.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     for (int e = 0; e < s->n; e++) {
-      const int* g = &gi[(size_t)e * GI_TOTAL];
+      const int* g = &gi[(size_t)e * CTX_I + SM_I];
       if (ncon) ncon[e] = g[GI_NCON];
       if (nefc) {
         int rows = g[GI_NSIMPLE];
@@ -842,13 +870,12 @@ int adroit_overflow(adroit_sim* s, int64_t* out2_host, void* stream) {
 // debug: raw per-env scratch block (fp64 host buffer [n][count]) starting at T-offset `offset`; layout in csrc/model.cuh
 int adroit_debug_scratch(adroit_sim* s, int offset, int count, double* out_host, void* stream) {
   CK(cudaSetDevice(s->device));
-  if (!(s->f64 ? (void*)s->sd.dbg_scratch : (void*)s->sf.dbg_scratch)) FAIL("no introspection launch (set_state / get_frames / get_solver) has run yet");
-  return download_field(s, out_host, STF(dbg_scratch), count, G_TOTAL, offset, (cudaStream_t)stream);
+  return download_field(s, out_host, CTXP, count, CTX_T, SM_T + offset, (cudaStream_t)stream);
 }
 int adroit_debug_iscratch(adroit_sim* s, int32_t* out_host, void* stream) {
   CK(cudaSetDevice(s->device));
-  CK(cudaMemcpyAsync(out_host, s->f64 ? s->sd.iscratch : s->sf.iscratch, (size_t)s->n * GI_TOTAL * sizeof(int), cudaMemcpyDeviceToHost,
-                     (cudaStream_t)stream));
+  CK(cudaMemcpy2DAsync(out_host, GI_TOTAL * sizeof(int), (s->f64 ? s->sd.ctxi : s->sf.ctxi) + SM_I, CTX_I * sizeof(int), GI_TOTAL * sizeof(int),
+                       (size_t)s->n, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   CK(cudaStreamSynchronize((cudaStream_t)stream));
   return 0;
 }

@@ -52,10 +52,11 @@ template <typename T> DI T shape_lower_bound(int type, const T* R, const T* size
 }
 
 // ---------------------------------------------------------------- collision over the static candidate list
-template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned long long* overflow) {
+template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  const T *gpos = c.g + G_GPOS, *gmat = c.g + G_GMAT;
-  int* surv = c.si + I_SURV;
+  const T *gpos = c.template G<G_GPOS>(), *gmat = c.template G<G_GMAT>();
+  int* surv = c.template I<I_SURV>();
   const unsigned lt = (1u << c.lane) - 1u;
   int nsurv = 0;
   for (int base = 0; base < m.npair; base += 32) {
@@ -90,7 +91,7 @@ template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned
   }
   __syncwarp();
   int ncon = 0;
-  T* cmu = c.s + O_CMU;
+  T* cmu = c.template S<O_CMU>();
   for (int base = 0; base < nsurv; base += 32) {
     ConOut<T> out;
     out.n = 0;
@@ -120,7 +121,7 @@ template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned
     for (int q = 0; q < cnt; q++) {
       int ci = ncon + excl + q;
       if (ci >= MAXCON) break;
-      T* C = c.g + G_CON + 16 * ci;
+      T* C = c.template G<G_CON>() + 16 * ci;
       V3<T> pos = out.pos[q] + origin, x = normalized(out.nrm[q]);
       V3<T> y = (x.y > T(0.5) || x.y < T(-0.5)) ? mk<T>(0, 0, 1) : mk<T>(0, 1, 0);
       y = normalized(y - x * dot(x, y));
@@ -129,9 +130,9 @@ template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned
       C[1] = pos.x; C[2] = pos.y; C[3] = pos.z;
       C[4] = x.x; C[5] = x.y; C[6] = x.z; C[7] = y.x; C[8] = y.y; C[9] = y.z; C[10] = z.x; C[11] = z.y; C[12] = z.z;
       C[13] = m.pair_margin[k];
-      c.si[I_CDIM + ci] = m.pair_condim[k];
-      c.si[I_CB1 + ci] = m.geom_body[g1];
-      c.si[I_CB2 + ci] = m.geom_body[g2];
+      c.template I<I_CDIM>()[ci] = m.pair_condim[k];
+      c.template I<I_CB1>()[ci] = m.geom_body[g1];
+      c.template I<I_CB2>()[ci] = m.geom_body[g2];
       cmu[3 * ci] = m.pair_friction[5 * k];
       cmu[3 * ci + 1] = m.pair_friction[5 * k + 1];
       cmu[3 * ci + 2] = m.pair_friction[5 * k + 2];
@@ -152,11 +153,12 @@ template <typename T> __device__ __noinline__ void collision(Ctx<T>& c, unsigned
 // ---------------------------------------------------------------- constraint rows
 template <typename T> DI int n_edges(int dim) { return dim == 1 ? 1 : 2 * (dim - 1); }
 
-template <typename T> __device__ __noinline__ void make_constraint(Ctx<T>& c, unsigned long long* overflow) {
+template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* overflow) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  const T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL);
-  int* sinfo = c.si + I_SINFO;
-  T *sD = c.s + O_SD, *saref = c.s + O_SAREF, *sfl = c.s + O_SFL, *sforce = c.s + O_SFORCE;
+  const T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>();
+  int* sinfo = c.template I<I_SINFO>();
+  T *sD = c.template S<O_SD>(), *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>(), *sforce = c.template S<O_SFORCE>();
   const unsigned lt = (1u << c.lane) - 1u;
   T K, B;
   sol_KB(m, K, B);
@@ -233,12 +235,12 @@ template <typename T> __device__ __noinline__ void make_constraint(Ctx<T>& c, un
   c.nsimple = nrow;
 
   // contacts: contact-frame Jacobian rows (both layouts), frame velocity, impedance
-  const T *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS;
-  T *JR = c.g + G_JR, *JT = c.g + G_JT;
-  T *cD = c.s + O_CD, *cmu = c.s + O_CMU, *carefn = c.s + O_CAREFN, *cbt = c.s + O_CBT, *ef = c.s + O_EF;
+  const T *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>();
+  T *JR = c.template G<G_JR>(), *JT = c.template G<G_JT>();
+  T *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>(), *ef = c.template S<O_EF>();
   for (int ci = 0; ci < c.ncon; ci++) {
-    const T* C = c.g + G_CON + 16 * ci;
-    int b1 = c.si[I_CB1 + ci], b2 = c.si[I_CB2 + ci], dim = c.si[I_CDIM + ci];
+    const T* C = c.template G<G_CON>() + 16 * ci;
+    int b1 = c.template I<I_CB1>()[ci], b2 = c.template I<I_CB2>()[ci], dim = c.template I<I_CDIM>()[ci];
     unsigned long long m1 = m.body_dofmask[b1], m2 = m.body_dofmask[b2];
     T vsum[4] = {0, 0, 0, 0};
     for (int j = c.lane; j < NVP; j += 32) {
@@ -297,8 +299,9 @@ template <typename T> DI T simple_dot(const DModel<T>& m, int info, const T* x) 
   return up ? -s : s;
 }
 // contact-frame products  out[ci][a] = Jf[ci][a] . x   (lanes over rows, dof-major layout -> coalesced)
-template <typename T> DI void contact_frame_mul(Ctx<T>& c, const T* x, T* out) {
-  const T* JT = c.g + G_JT;
+template <class CX> DI void contact_frame_mul(CX& c, const typename CX::real* x, typename CX::real* out) {
+  using T = typename CX::real;
+  const T* JT = c.template G<G_JT>();
   int nrows = 4 * c.ncon;
   for (int r = c.lane; r < nrows; r += 32) {
     T s = 0;
@@ -316,11 +319,12 @@ template <typename T> DI T edge_val(const T* fx, const T* mu, int dim, int e, T&
 
 // cost, forces and states at the point whose frame accelerations are in O_AC and dof accelerations in `qacc`.
 // Returns the constraint cost (all lanes).  Also accumulates J^T f into V_QFC when `want_qfc`.
-template <typename T> __device__ __noinline__ T constraint_update(Ctx<T>& c, const T* qacc, bool want_qfc) {
+template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const typename CX::real* qacc, bool want_qfc) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  int* sinfo = c.si + I_SINFO;
-  const T *sD = c.s + O_SD, *saref = c.s + O_SAREF, *sfl = c.s + O_SFL;
-  T *sforce = c.s + O_SFORCE, *qfc = c.v(V_QFC);
+  int* sinfo = c.template I<I_SINFO>();
+  const T *sD = c.template S<O_SD>(), *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>();
+  T *sforce = c.template S<O_SFORCE>(), *qfc = c.template V<V_QFC>();
   T cost = 0;
   if (want_qfc) {
     for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
@@ -351,10 +355,10 @@ template <typename T> __device__ __noinline__ T constraint_update(Ctx<T>& c, con
     }
   }
   // contacts: one lane per contact walks its edges; builds the 4x4 Hessian weight W and the frame force
-  const T *ac = c.s + O_AC, *cD = c.s + O_CD, *cmu = c.s + O_CMU, *carefn = c.s + O_CAREFN, *cbt = c.s + O_CBT;
-  T *ef = c.s + O_EF, *W = c.s + O_W;
+  const T *ac = c.template S<O_AC>(), *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>();
+  T *ef = c.template S<O_EF>(), *W = c.template S<O_W>();
   for (int ci = c.lane; ci < c.ncon; ci += 32) {
-    int dim = c.si[I_CDIM + ci], ne = n_edges<T>(dim);
+    int dim = c.template I<I_CDIM>()[ci], ne = n_edges<T>(dim);
     T D = cD[ci], w[7] = {0, 0, 0, 0, 0, 0, 0};
     for (int e = 0; e < ne; e++) {
       T sign;
@@ -376,9 +380,9 @@ template <typename T> __device__ __noinline__ T constraint_update(Ctx<T>& c, con
   __syncwarp();
   if (want_qfc && c.ncon > 0) {
     // frame forces F[ci][4] into O_AV (scratch use), then qfc[j] += sum_r Jr[r][j] F[r]
-    T* F = c.s + O_AV;
+    T* F = c.template S<O_AV>();
     for (int ci = c.lane; ci < c.ncon; ci += 32) {
-      int dim = c.si[I_CDIM + ci];
+      int dim = c.template I<I_CDIM>()[ci];
       const T* f = ef + 6 * ci;
       if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
       else {
@@ -389,7 +393,7 @@ template <typename T> __device__ __noinline__ T constraint_update(Ctx<T>& c, con
       }
     }
     __syncwarp();
-    const T* JR = c.g + G_JR;
+    const T* JR = c.template G<G_JR>();
     for (int j = c.lane; j < m.nv; j += 32) {
       T s = 0;
       for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
@@ -401,10 +405,11 @@ template <typename T> __device__ __noinline__ T constraint_update(Ctx<T>& c, con
 }
 
 // derivative pair (f', f'') of the constraint cost along qacc + alpha*search
-template <typename T> DI void ls_eval(Ctx<T>& c, T alpha, const T* qacc, const T* search, T& d1, T& d2) {
+template <class CX> DI void ls_eval(CX& c, typename CX::real alpha, const typename CX::real* qacc, const typename CX::real* search, typename CX::real& d1, typename CX::real& d2) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  const int* sinfo = c.si + I_SINFO;
-  const T *sD = c.s + O_SD, *saref = c.s + O_SAREF, *sfl = c.s + O_SFL;
+  const int* sinfo = c.template I<I_SINFO>();
+  const T *sD = c.template S<O_SD>(), *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>();
   T a = 0, b = 0;
   for (int r = c.lane; r < c.nsimple; r += 32) {
     int info = sinfo[r] & 0x1fff;
@@ -416,9 +421,9 @@ template <typename T> DI void ls_eval(Ctx<T>& c, T alpha, const T* qacc, const T
       else { a += D * z * y; b += D * y * y; }
     } else if (z < 0) { a += D * z * y; b += D * y * y; }
   }
-  const T *ac = c.s + O_AC, *av = c.s + O_AV, *cD = c.s + O_CD, *cmu = c.s + O_CMU, *carefn = c.s + O_CAREFN, *cbt = c.s + O_CBT;
+  const T *ac = c.template S<O_AC>(), *av = c.template S<O_AV>(), *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>();
   for (int t = c.lane; t < 6 * c.ncon; t += 32) {
-    int ci = t / 6, e = t - 6 * ci, dim = c.si[I_CDIM + ci];
+    int ci = t / 6, e = t - 6 * ci, dim = c.template I<I_CDIM>()[ci];
     if (e >= n_edges<T>(dim)) continue;
     T sign;
     int k;
@@ -433,13 +438,14 @@ template <typename T> DI void ls_eval(Ctx<T>& c, T alpha, const T* qacc, const T
 }
 
 // H (packed, O_H) = M + J^T D_active J, using the states / weights left by constraint_update
-template <typename T> __device__ __noinline__ void build_hessian(Ctx<T>& c) {
+template <class CX> PHASE_FN void build_hessian(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  T *H = c.s + O_H, *M = c.s + O_M;
+  T *H = c.template S<O_H>(), *M = c.template S<O_M>();
   for (int p = c.lane; p < NTRI; p += 32) H[p] = M[p];
   __syncwarp();
-  const int* sinfo = c.si + I_SINFO;
-  const T* sD = c.s + O_SD;
+  const int* sinfo = c.template I<I_SINFO>();
+  const T* sD = c.template S<O_SD>();
   for (int r = c.lane; r < c.nsimple; r += 32) {
     int info = sinfo[r];
     if (!((info >> 13) & 1)) continue;
@@ -455,7 +461,7 @@ template <typename T> __device__ __noinline__ void build_hessian(Ctx<T>& c) {
     }
   }
   __syncwarp();
-  const T *JR = c.g + G_JR, *W = c.s + O_W;
+  const T *JR = c.template G<G_JR>(), *W = c.template S<O_W>();
   for (int ci = 0; ci < c.ncon; ci++) {
     const T* w = W + 7 * ci;
     if (w[0] == 0) continue;  // no active edge (warp-uniform: shared memory value)
@@ -500,12 +506,13 @@ template <typename T> __device__ __noinline__ void build_hessian(Ctx<T>& c) {
 }
 
 // ---------------------------------------------------------------- Newton solver (primal, exact line search)
-template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
+template <class CX> PHASE_FN void newton(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
   const int nv = m.nv, lane = c.lane;
-  T *qacc = c.v(V_QACC), *Ma = c.v(V_MA), *grad = c.v(V_GRAD), *search = c.v(V_SEARCH), *Mv = c.v(V_MV), *qfc = c.v(V_QFC);
-  const T *qfs = c.v(V_QFS), *qas = c.v(V_QAS), *warm = c.v(V_WARM);
-  T *M = c.s + O_M, *H = c.s + O_H, *ac = c.s + O_AC, *av = c.s + O_AV;
+  T *qacc = c.template V<V_QACC>(), *Ma = c.template V<V_MA>(), *grad = c.template V<V_GRAD>(), *search = c.template V<V_SEARCH>(), *Mv = c.template V<V_MV>(), *qfc = c.template V<V_QFC>();
+  const T *qfs = c.template V<V_QFS>(), *qas = c.template V<V_QAS>(), *warm = c.template V<V_WARM>();
+  T *M = c.template S<O_M>(), *H = c.template S<O_H>(), *ac = c.template S<O_AC>(), *av = c.template S<O_AV>();
   const T scale = T(1) / (m.meaninertia * (nv > 1 ? nv : 1));
 
   // cost at the warm start and at qacc_smooth (Gauss term vanishes there)
@@ -540,8 +547,8 @@ template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
     g2 = warp_sum(g2);
     if (scale * sqrt(g2) < m.tolerance) break;
     build_hessian(c);
-    chol_dense(H, c.v(V_DINV), nv, lane);
-    chol_solve(H, c.v(V_DINV), search, nv, lane);
+    chol_dense(H, c.template V<V_DINV>(), nv, lane);
+    chol_solve(H, c.template V<V_DINV>(), search, nv, lane);
     symv(M, search, Mv, nv, lane);
     contact_frame_mul(c, search, av);
     __syncwarp();
@@ -586,20 +593,21 @@ template <typename T> __device__ __noinline__ void newton(Ctx<T>& c) {
 }
 
 // ---------------------------------------------------------------- noslip (Gauss-Seidel on friction rows, matrix-free)
-template <typename T> __device__ __noinline__ void noslip(Ctx<T>& c) {
+template <class CX> PHASE_FN void noslip(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
   const int nv = m.nv, lane = c.lane;
-  const T *Minv = c.g + G_MINV, *JR = c.g + G_JR, *qas = c.v(V_QAS);
-  T *u = c.v(V_GRAD), *tmp = c.v(V_SEARCH), *qfc = c.v(V_QFC), *YT = c.g + G_YT;
-  const int* sinfo = c.si + I_SINFO;
-  const T *saref = c.s + O_SAREF, *sfl = c.s + O_SFL, *cmu = c.s + O_CMU, *cbt = c.s + O_CBT;
-  T *sforce = c.s + O_SFORCE, *ef = c.s + O_EF;
+  const T *Minv = c.template G<G_MINV>(), *JR = c.template G<G_JR>(), *qas = c.template V<V_QAS>();
+  T *u = c.template V<V_GRAD>(), *tmp = c.template V<V_SEARCH>(), *qfc = c.template V<V_QFC>(), *YT = c.template G<G_YT>();
+  const int* sinfo = c.template I<I_SINFO>();
+  const T *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>(), *cmu = c.template S<O_CMU>(), *cbt = c.template S<O_CBT>();
+  T *sforce = c.template S<O_SFORCE>(), *ef = c.template S<O_EF>();
   // u = M^-1 J^T f  (qfc holds J^T f from the last constraint_update)
   symv(Minv, qfc, u, nv, lane);
   // Yt[ci][k] = M^-1 Jt_k^T and K1 = 4 mu_k^2 Jt_k.Yt_k (kept in O_AV[ci*4+1+k])
-  T* K1 = c.s + O_AV;
+  T* K1 = c.template S<O_AV>();
   for (int ci = 0; ci < c.ncon; ci++) {
-    int dim = c.si[I_CDIM + ci];
+    int dim = c.template I<I_CDIM>()[ci];
     for (int k = 0; k + 2 <= dim && k < 3; k++) {
       const T* Jt = JR + (4 * ci + 1 + k) * NVP;
       for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
@@ -634,7 +642,7 @@ template <typename T> __device__ __noinline__ void noslip(Ctx<T>& c) {
       __syncwarp();
     }
     for (int ci = 0; ci < c.ncon; ci++) {
-      int dim = c.si[I_CDIM + ci];
+      int dim = c.template I<I_CDIM>()[ci];
       for (int k = 0; k + 2 <= dim && k < 3; k++) {
         const T* Jt = JR + (4 * ci + 1 + k) * NVP;
         T s = 0;
@@ -663,11 +671,12 @@ template <typename T> __device__ __noinline__ void noslip(Ctx<T>& c) {
 }
 
 // qfrc_constraint = J^T f from the stored forces (V_QFC)
-template <typename T> __device__ __noinline__ void constraint_force(Ctx<T>& c) {
+template <class CX> PHASE_FN void constraint_force(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  T *qfc = c.v(V_QFC), *F = c.s + O_AV;
-  const int* sinfo = c.si + I_SINFO;
-  const T *sforce = c.s + O_SFORCE, *ef = c.s + O_EF, *cmu = c.s + O_CMU;
+  T *qfc = c.template V<V_QFC>(), *F = c.template S<O_AV>();
+  const int* sinfo = c.template I<I_SINFO>();
+  const T *sforce = c.template S<O_SFORCE>(), *ef = c.template S<O_EF>(), *cmu = c.template S<O_CMU>();
   for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
   __syncwarp();
   for (int r = c.lane; r < c.nsimple; r += 32) {
@@ -683,7 +692,7 @@ template <typename T> __device__ __noinline__ void constraint_force(Ctx<T>& c) {
       }
   }
   for (int ci = c.lane; ci < c.ncon; ci += 32) {
-    int dim = c.si[I_CDIM + ci];
+    int dim = c.template I<I_CDIM>()[ci];
     const T* f = ef + 6 * ci;
     if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
     else {
@@ -694,7 +703,7 @@ template <typename T> __device__ __noinline__ void constraint_force(Ctx<T>& c) {
     }
   }
   __syncwarp();
-  const T* JR = c.g + G_JR;
+  const T* JR = c.template G<G_JR>();
   for (int j = c.lane; j < m.nv; j += 32) {
     T s = 0;
     for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
@@ -730,19 +739,20 @@ template <typename T> DI bool ray_hits_cylinder(const T* spos, const T* smat, co
     }
   return false;
 }
-template <typename T> __device__ __noinline__ T touch_sensor(Ctx<T>& c) {
+template <class CX> PHASE_FN typename CX::real touch_sensor(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
   if (m.touch_site < 0) return T(0);
   int sb = m.site_body[m.touch_site];
-  const T *ef = c.s + O_EF, *spos = c.g + G_SPOS + 3 * m.touch_site, *smat = c.s + O_XMAT + 9 * sb;
+  const T *ef = c.template S<O_EF>(), *spos = c.template G<G_SPOS>() + 3 * m.touch_site, *smat = c.template S<O_XMAT>() + 9 * sb;
   T sum = 0;
   for (int ci = c.lane; ci < c.ncon; ci += 32) {
-    int b1 = c.si[I_CB1 + ci], b2 = c.si[I_CB2 + ci], dim = c.si[I_CDIM + ci];
+    int b1 = c.template I<I_CB1>()[ci], b2 = c.template I<I_CB2>()[ci], dim = c.template I<I_CDIM>()[ci];
     if (sb != b1 && sb != b2) continue;
     T fn = 0;
     for (int e = 0; e < n_edges<T>(dim); e++) fn += ef[6 * ci + e];
     if (fn <= 0) continue;
-    const T* C = c.g + G_CON + 16 * ci;
+    const T* C = c.template G<G_CON>() + 16 * ci;
     T sgn = sb == b2 ? T(-1) : T(1), ray[3] = {sgn * C[4], sgn * C[5], sgn * C[6]};
     if (ray_hits_cylinder(spos, smat, m.touch_size, C + 1, ray)) sum += fn;
   }

@@ -15,18 +15,94 @@
 
 namespace adroit {
 
-template <typename T> struct Ctx {
+// Per-env context block in global memory: the "S part" (what the single-kernel design kept in shared memory; offsets
+// O_*, V_* of model.cuh) followed by the "G part" (offsets G_*).  Every phase kernel names, in a MAP, the regions it
+// wants staged in shared memory; everything else is addressed in the context block directly (L1/L2).  The accessors
+// resolve at compile time, so a device function works unchanged whichever side a region lives on.
+constexpr int CTX_T = SM_T + G_TOTAL;     // T words per env
+constexpr int CTX_I = SM_I + GI_TOTAL;    // int words per env
+enum { R_IN = 1, R_OUT = 2, R_ZERO = 4 };
+struct Reg { int off, len, flags; };
+constexpr int pad4(int x) { return (x + 3) / 4 * 4; }
+template <class MAP> constexpr int map_soff(int O) {
+  int acc = 0;
+  for (int i = 0; i < MAP::NT; i++) {
+    if (O >= MAP::RT[i].off && O < MAP::RT[i].off + MAP::RT[i].len) return acc + (O - MAP::RT[i].off);
+    acc += pad4(MAP::RT[i].len);
+  }
+  return -1;
+}
+template <class MAP> constexpr int map_ioff(int O) {
+  int acc = 0;
+  for (int i = 0; i < MAP::NI; i++) {
+    if (O >= MAP::RI[i].off && O < MAP::RI[i].off + MAP::RI[i].len) return acc + (O - MAP::RI[i].off);
+    acc += pad4(MAP::RI[i].len);
+  }
+  return -1;
+}
+template <class MAP> constexpr int map_st() { int a = 0; for (int i = 0; i < MAP::NT; i++) a += pad4(MAP::RT[i].len); return a; }
+template <class MAP> constexpr int map_si() { int a = 0; for (int i = 0; i < MAP::NI; i++) a += pad4(MAP::RI[i].len); return a; }
+template <typename T, class MAP> constexpr size_t map_bytes() { return map_st<MAP>() * sizeof(T) + map_si<MAP>() * sizeof(int); }
+
+template <typename T_, class MAP_> struct Ctx {
+  using real = T_;
+  using MAP = MAP_;
+  typedef T_ T;
   const DModel<T>& m;
-  T* s;      // shared memory slice (T)
-  int* si;   // shared memory slice (int)
-  T* g;      // global scratch of this env
-  int* gi;   // int scratch of this env
+  T* sm;     // this warp's shared-memory slice (T regions of MAP)
+  int* smi;  // this warp's shared-memory slice (int regions of MAP)
+  T* gb;     // this env's context block (T)
+  int* gib;  // this env's context block (int): [SM_I | GI_TOTAL]
+  int* gi;   // = gib + SM_I
   int lane;
   int ncon, nsimple;
-  __device__ Ctx(const DModel<T>& mm, T* s_, int* si_, T* g_, int* gi_, int lane_)
-      : m(mm), s(s_), si(si_), g(g_), gi(gi_), lane(lane_), ncon(0), nsimple(0) {}
-  DI T* v(int k) const { return s + k * NVP; }
+  __device__ Ctx(const DModel<T>& mm, T* sm_, int* smi_, T* gb_, int* gib_, int lane_)
+      : m(mm), sm(sm_), smi(smi_), gb(gb_), gib(gib_), gi(gib_ + SM_I), lane(lane_), ncon(0), nsimple(0) {}
+  template <int O> static constexpr bool in_smem() { return map_soff<MAP>(O) >= 0; }
+  template <int O> DI T* S() const {
+    constexpr int so = map_soff<MAP>(O);
+    if constexpr (so >= 0) return sm + so;
+    else return gb + O;
+  }
+  template <int K> DI T* V() const { return S<K * NVP>(); }
+  template <int O> DI T* G() const { return S<SM_T + O>(); }
+  template <int O> DI int* I() const {
+    constexpr int so = map_ioff<MAP>(O);
+    if constexpr (so >= 0) return smi + so;
+    else return gib + O;
+  }
 };
+
+// stage the MAP's regions between the context block and shared memory (whole warp, coalesced)
+template <class CX, int I = 0> DI void stage_in(CX& c) {
+  using MAP = typename CX::MAP;
+  if constexpr (I < MAP::NT) {
+    constexpr Reg r = MAP::RT[I];
+    constexpr int so = map_soff<MAP>(r.off);
+    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane; j < r.len; j += 32) c.sm[so + j] = c.gb[r.off + j]; }
+    else if constexpr ((r.flags & R_ZERO) != 0) { for (int j = c.lane; j < r.len; j += 32) c.sm[so + j] = 0; }
+    stage_in<CX, I + 1>(c);
+  } else if constexpr (I < MAP::NT + MAP::NI) {
+    constexpr Reg r = MAP::RI[I - MAP::NT];
+    constexpr int so = map_ioff<MAP>(r.off);
+    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane; j < r.len; j += 32) c.smi[so + j] = c.gib[r.off + j]; }
+    stage_in<CX, I + 1>(c);
+  }
+}
+template <class CX, int I = 0> DI void stage_out(CX& c) {
+  using MAP = typename CX::MAP;
+  if constexpr (I < MAP::NT) {
+    constexpr Reg r = MAP::RT[I];
+    constexpr int so = map_soff<MAP>(r.off);
+    if constexpr ((r.flags & R_OUT) != 0) { for (int j = c.lane; j < r.len; j += 32) c.gb[r.off + j] = c.sm[so + j]; }
+    stage_out<CX, I + 1>(c);
+  } else if constexpr (I < MAP::NT + MAP::NI) {
+    constexpr Reg r = MAP::RI[I - MAP::NT];
+    constexpr int so = map_ioff<MAP>(r.off);
+    if constexpr ((r.flags & R_OUT) != 0) { for (int j = c.lane; j < r.len; j += 32) c.gib[r.off + j] = c.smi[so + j]; }
+    stage_out<CX, I + 1>(c);
+  }
+}
 
 template <typename T> DI void quat_mul(T* r, const T* a, const T* b) {
   T w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
@@ -61,10 +137,11 @@ template <> DI void sincos_t<float>(float x, float* s, float* c) { sincosf(x, s,
 template <> DI void sincos_t<double>(double x, double* s, double* c) { sincos(x, s, c); }
 
 // ---------------------------------------------------------------- kinematics (level-synchronous over the body tree)
-template <typename T> __device__ __noinline__ void kinematics(Ctx<T>& c) {
+template <class CX> PHASE_FN void kinematics(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  T *xpos = c.s + O_XPOS, *xquat = c.s + O_XQUAT, *xmat = c.s + O_XMAT, *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS;
-  const T *par = c.s + O_PAR, *qpos = c.v(V_QPOS);
+  T *xpos = c.template S<O_XPOS>(), *xquat = c.template S<O_XQUAT>(), *xmat = c.template S<O_XMAT>(), *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>();
+  const T *par = c.template S<O_PAR>(), *qpos = c.template V<V_QPOS>();
   if (c.lane == 0) {
     xpos[0] = xpos[1] = xpos[2] = 0;
     xquat[0] = 1; xquat[1] = xquat[2] = xquat[3] = 0;
@@ -115,27 +192,28 @@ template <typename T> __device__ __noinline__ void kinematics(Ctx<T>& c) {
 }
 
 // geom / site world frames (global scratch) and single-body inertias about the body origin
-template <typename T> __device__ __noinline__ void frames_and_inertia(Ctx<T>& c) {
+template <class CX> PHASE_FN void frames_and_inertia(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  const T *xpos = c.s + O_XPOS, *xmat = c.s + O_XMAT, *par = c.s + O_PAR;
+  const T *xpos = c.template S<O_XPOS>(), *xmat = c.template S<O_XMAT>(), *par = c.template S<O_PAR>();
   for (int g = c.lane; g < m.ngeom; g += 32) {
     int b = m.geom_body[g];
     T t[3];
     rot(t, xmat + 9 * b, m.geom_pos + 3 * g);
-    for (int i = 0; i < 3; i++) c.g[G_GPOS + 3 * g + i] = xpos[3 * b + i] + t[i];
+    for (int i = 0; i < 3; i++) c.template G<G_GPOS>()[3 * g + i] = xpos[3 * b + i] + t[i];
     const T *A = xmat + 9 * b, *B = m.geom_mat + 9 * g;
     for (int i = 0; i < 3; i++)
-      for (int j = 0; j < 3; j++) c.g[G_GMAT + 9 * g + 3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+      for (int j = 0; j < 3; j++) c.template G<G_GMAT>()[9 * g + 3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
   }
   for (int sidx = c.lane; sidx < m.nsite; sidx += 32) {
     int b = m.site_body[sidx], so = m.site_par[sidx];
     T sp[3], t[3];
     for (int i = 0; i < 3; i++) sp[i] = so >= 0 ? par[so + i] : m.site_pos[3 * sidx + i];
     rot(t, xmat + 9 * b, sp);
-    for (int i = 0; i < 3; i++) c.g[G_SPOS + 3 * sidx + i] = xpos[3 * b + i] + t[i];
+    for (int i = 0; i < 3; i++) c.template G<G_SPOS>()[3 * sidx + i] = xpos[3 * b + i] + t[i];
   }
   // inertia {m, h[3] = m*c, I[6] = xx,yy,zz,xy,xz,yz} about xpos[b], world axes
-  T* crb = c.s + O_CRB;
+  T* crb = c.template S<O_CRB>();
   for (int b = c.lane; b < m.nbody; b += 32) {
     T mass = m.body_mass[b], Rw[9], cv[3];
     const T *A = xmat + 9 * b, *B = m.body_imat + 9 * b, *dg = m.body_inertia + 3 * b;
@@ -152,7 +230,7 @@ template <typename T> __device__ __noinline__ void frames_and_inertia(Ctx<T>& c)
       I[e] = v;
     }
     T out[10] = {mass, mass * cv[0], mass * cv[1], mass * cv[2], I[0], I[1], I[2], I[3], I[4], I[5]};
-    for (int e = 0; e < 10; e++) { crb[10 * b + e] = out[e]; c.g[G_CIN + 10 * b + e] = out[e]; }
+    for (int e = 0; e < 10; e++) { crb[10 * b + e] = out[e]; c.template G<G_CIN>()[10 * b + e] = out[e]; }
   }
   __syncwarp();
 }
@@ -183,10 +261,11 @@ template <typename T> DI void dof_motion(const DModel<T>& m, const T* xanc, cons
 }
 
 // composite inertias (children folded into parents, deepest level first) and the joint-space inertia matrix
-template <typename T> __device__ __noinline__ void mass_matrix(Ctx<T>& c) {
+template <class CX> PHASE_FN void mass_matrix(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  T *crb = c.s + O_CRB, *M = c.s + O_M;
-  const T *xpos = c.s + O_XPOS, *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS;
+  T *crb = c.template S<O_CRB>(), *M = c.template S<O_M>();
+  const T *xpos = c.template S<O_XPOS>(), *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>();
   for (int L = m.nlevel - 1; L >= 1; L--) {
     int beg = m.level_start[L - 1], end = m.level_start[L];
     for (int idx = beg + c.lane; idx < end; idx += 32) {
@@ -232,10 +311,11 @@ template <typename T> __device__ __noinline__ void mass_matrix(Ctx<T>& c) {
 }
 
 // recursive Newton-Euler: bias forces (Coriolis + centrifugal + gravity) into V_T1
-template <typename T> __device__ __noinline__ void rne_bias(Ctx<T>& c) {
+template <class CX> PHASE_FN void rne_bias(CX& c) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  const T *xpos = c.s + O_XPOS, *xanc = c.s + O_XANC, *xaxis = c.s + O_XAXIS, *qvel = c.v(V_QVEL);
-  T *vel = c.g + G_VEL, *acc = c.g + G_ACC, *frc = c.g + G_FRC;
+  const T *xpos = c.template S<O_XPOS>(), *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>(), *qvel = c.template V<V_QVEL>();
+  T *vel = c.template G<G_VEL>(), *acc = c.template G<G_ACC>(), *frc = c.template G<G_FRC>();
   if (c.lane == 0) {
     for (int i = 0; i < 6; i++) { vel[i] = 0; frc[i] = 0; }
     acc[0] = acc[1] = acc[2] = 0;
@@ -268,7 +348,7 @@ template <typename T> __device__ __noinline__ void rne_bias(Ctx<T>& c) {
         for (int i = 0; i < 6; i++) v[i] += vj[i];
       }
       for (int i = 0; i < 6; i++) { vel[6 * b + i] = v[i]; acc[6 * b + i] = a[i]; }
-      const T* I = c.g + G_CIN + 10 * b;
+      const T* I = c.template G<G_CIN>() + 10 * b;
       T Ia[6], Iv[6], f[6], u[3];
       inert_mul(Ia, I, a);
       inert_mul(Iv, I, v);
@@ -298,7 +378,7 @@ template <typename T> __device__ __noinline__ void rne_bias(Ctx<T>& c) {
     }
     __syncwarp();
   }
-  T* bias = c.v(V_T1);
+  T* bias = c.template V<V_T1>();
   for (int j = c.lane; j < m.nv; j += 32) {
     int b = m.dof_body[j];
     T S[6];
@@ -366,7 +446,7 @@ template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1,
 // in-place Cholesky A = L L^T; dinv[j] = 1 / L[j][j].  Leading min(n,32) block: left-looking by columns, lane = row,
 // vectorised dot products.  Rows 32..n-1 (n <= 36) are "bordered" on afterwards: each is one forward substitution
 // against the leading factor plus a few warp-wide dot products, instead of doubling every column step for 1-4 rows.
-template <typename T> __device__ __noinline__ void chol_dense(T* A, T* dinv, int n, int lane) {
+template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, int n, int lane) {
   const int nb = n < 32 ? n : 32;
   T* r0 = A + rowoff(lane);
   for (int j = 0; j < nb; j++) {
@@ -428,7 +508,7 @@ template <typename T> DI void chol_solve(const T* L, const T* dinv, T* x, int n,
 // only if i is an ancestor dof of k): eliminating leaves first creates no fill-in (Featherstone; MuJoCo's mj_factorM
 // uses the same order).  One step per dof, its (ancestor, ancestor) pair updates spread over the lanes; the schedule
 // ld_start / ld_pair is built on the host.  On return: strict lower part = L, diagonal = D, dinv = 1/D.
-template <typename T> __device__ __noinline__ void ltdl_factor(const DModel<T>& m, T* A, T* dinv, int lane) {
+template <typename T> PHASE_FN void ltdl_factor(const DModel<T>& m, T* A, T* dinv, int lane) {
   const int n = m.nv;
   for (int k = n - 1; k >= 0; k--) {
     const T* rk = A + rowoff(k);
@@ -460,7 +540,7 @@ template <typename T> DI void ltdl_solve(const T* L, const T* dinv, T* x, int n,
 }
 // M^-1 = W D^-1 W^T with W = L^-1 (unit lower, same ancestor pattern): W by depth levels (wl_pair, levels padded to
 // whole warps), then every entry of M^-1 as a short sum over the common ancestors of its two dofs (lca table).
-template <typename T> __device__ __noinline__ void minv_tree(const DModel<T>& m, const T* L, const T* dinv, T* W, T* Minv, int lane) {
+template <typename T> PHASE_FN void minv_tree(const DModel<T>& m, const T* L, const T* dinv, T* W, T* Minv, int lane) {
   for (int p = lane; p < NTRI; p += 32) { W[p] = 0; Minv[p] = 0; }
   __syncwarp();
   for (int base = 0; base < m.n_wl; base += 32) {
@@ -490,7 +570,7 @@ template <typename T> __device__ __noinline__ void minv_tree(const DModel<T>& m,
 }
 
 // y = A x for a symmetric matrix (lower storage); x, y in shared memory, y != x
-template <typename T> __device__ __noinline__ void symv(const T* A, const T* x, T* y, int n, int lane) {
+template <typename T> SUB_FN void symv(const T* A, const T* x, T* y, int n, int lane) {
   T y0 = 0, y1 = 0;
   const int i0 = lane, i1 = lane + 32;
   if (i0 < n) {
@@ -519,10 +599,11 @@ template <typename T> __device__ __noinline__ void symv(const T* A, const T* x, 
 template <typename T> DI T sym_get(const T* A, int i, int j) { return i >= j ? A[tri(i, j)] : A[tri(j, i)]; }
 
 // passive + actuation + qfrc_smooth + qacc_smooth (+ M^-1 for the noslip pass); M stays in O_M, O_H is scratch
-template <typename T> __device__ __noinline__ void smooth_dynamics(Ctx<T>& c, bool need_minv) {
+template <class CX> PHASE_FN void smooth_dynamics(CX& c, bool need_minv) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
-  const T *qpos = c.v(V_QPOS), *qvel = c.v(V_QVEL), *bias = c.v(V_T1), *ctrl = c.v(V_CTRL);
-  T *qfs = c.v(V_QFS), *qas = c.v(V_QAS), *act = c.v(V_T2);
+  const T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *bias = c.template V<V_T1>(), *ctrl = c.template V<V_CTRL>();
+  T *qfs = c.template V<V_QFS>(), *qas = c.template V<V_QAS>(), *act = c.template V<V_T2>();
   for (int j = c.lane; j < m.nv; j += 32) act[j] = 0;
   __syncwarp();
   for (int u = c.lane; u < m.nu; u += 32) {
@@ -535,14 +616,14 @@ template <typename T> __device__ __noinline__ void smooth_dynamics(Ctx<T>& c, bo
     T f = -m.dof_damping[j] * qvel[j] - bias[j] + act[j];
     qfs[j] = f;
     qas[j] = f;
-    c.g[G_DBG_BIAS + j] = bias[j];
+    c.template G<G_DBG_BIAS>()[j] = bias[j];
   }
-  T *M = c.s + O_M, *H = c.s + O_H;
+  T *M = c.template S<O_M>(), *H = c.template S<O_H>();
   for (int p = c.lane; p < NTRI; p += 32) H[p] = M[p];
   __syncwarp();
-  ltdl_factor(m, H, c.v(V_DINV), c.lane);
-  ltdl_solve(H, c.v(V_DINV), qas, m.nv, c.lane);
-  if (need_minv) minv_tree(m, H, c.v(V_DINV), c.g + G_LINV, c.g + G_MINV, c.lane);
+  ltdl_factor(m, H, c.template V<V_DINV>(), c.lane);
+  ltdl_solve(H, c.template V<V_DINV>(), qas, m.nv, c.lane);
+  if (need_minv) minv_tree(m, H, c.template V<V_DINV>(), c.template G<G_LINV>(), c.template G<G_MINV>(), c.lane);
 }
 
 }  // namespace adroit

@@ -14,6 +14,10 @@ enum { G_PLANE = 0, G_SPHERE = 2, G_CAPSULE = 3, G_CYLINDER = 5, G_BOX = 6 };
 
 template <typename T> struct V3 { T x, y, z; };
 #define DI __device__ __forceinline__
+// phase functions are inlined into their phase kernel (one call site each): address spaces and model-table loads
+// resolve statically (LDS / LDG / LDC instead of generic loads); SUB_FN marks helpers with several call sites
+#define PHASE_FN __device__ __forceinline__
+#define SUB_FN __device__ __noinline__
 
 template <typename T> DI V3<T> mk(T x, T y, T z) { V3<T> r; r.x = x; r.y = y; r.z = z; return r; }
 template <typename T> DI V3<T> operator+(V3<T> a, V3<T> b) { return mk<T>(a.x + b.x, a.y + b.y, a.z + b.z); }

@@ -118,15 +118,16 @@ template <typename T> struct DModel {
   int any_damping;
 };
 
-// persistent per-env state + I/O pointers handed to the kernels
+// persistent per-env state handed to the kernels.  qpos / qvel / qacc_warmstart / ctrl / per-env model parameters /
+// cached task frames live INSIDE the context block (V_QPOS, V_QVEL, V_WARM, V_CTRL, O_PAR, O_TF regions).
 template <typename T> struct DState {
   int n;
-  T *qpos, *qvel, *warm, *ctrl, *par, *tf;   // [n][NVP] x4, [n][NPARP], [n][NTF]
-  T *scratch, *dbg_scratch;                 // [resident warps][G_TOTAL]; [n][G_TOTAL], allocated by the first debug launch
-  int* iscratch;                                // [n][GI_TOTAL]
+  T* ctx;                                       // [n][CTX_T]   (dynamics.cuh)
+  int* ctxi;                                    // [n][CTX_I]
   int *t, *episode, *ep_goal;                   // [n]
   T* ep_return;                                 // [n]
   double* acc;                                  // [n][4]: sum return, #any-goal, #goal>thr, #episodes
+  unsigned char* reset_flag;                    // [n] set by the step epilogue when AUTO_RESET wants a reset
   unsigned long long* overflow;                 // [2]
   unsigned long long seed;
   long long env_off;

@@ -53,11 +53,12 @@ template <typename T> DI void draw_params(const DModel<T>& m, unsigned long long
 
 // task frames cached after every forward (the reference reads data.site_xpos / body_xpos, which mujoco-py leaves at the
 // values of the LAST mj_forward, i.e. one substep behind qpos)
-template <typename T> DI void cache_task_frames(Ctx<T>& c, T touch) {
+template <class CX> DI void cache_task_frames(CX& c, typename CX::real touch) {
+  using T = typename CX::real;
   const DModel<T>& m = c.m;
   const int* ti = m.task_int;
-  const T *xpos = c.s + O_XPOS, *xquat = c.s + O_XQUAT, *spos = c.g + G_SPOS;
-  T* tf = c.s + O_TF;
+  const T *xpos = c.template S<O_XPOS>(), *xquat = c.template S<O_XQUAT>(), *spos = c.template G<G_SPOS>();
+  T* tf = c.template S<O_TF>();
   if (c.lane == 0) {
     auto cp = [&](int o, const T* src) { tf[o] = src[0]; tf[o + 1] = src[1]; tf[o + 2] = src[2]; };
     switch (m.task) {
