@@ -52,20 +52,22 @@ struct MapCollide {
   static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV, 0}};
 };
 struct MapSolve {
-  static constexpr int NT = 24, NI = 4;
+  static constexpr int NT = 24, NI = 5;
   static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_MA, R_ZERO),
                                  VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_QFC, R_ZERO | R_OUT), VR(V_DINV, R_ZERO),
                                  Reg{O_M, NTRI, R_IN}, Reg{O_H, NTRI, 0},
                                  Reg{O_SD, MAXSIMPLE, R_OUT}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
                                  Reg{O_AC, CROWS, 0}, Reg{O_AV, CROWS, 0}, Reg{O_CD, MAXCON, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
                                  Reg{O_CAREFN, MAXCON, 0}, Reg{O_CBT, MAXCON * 3, R_OUT}, Reg{O_EF, MAXCON * 6, R_OUT}, Reg{O_W, MAXCON * 7, 0}};
-  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MAXCON, R_IN}, Reg{I_CB1, MAXCON, R_IN}, Reg{I_CB2, MAXCON, R_IN}};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MAXCON, R_IN}, Reg{I_CB1, MAXCON, R_IN}, Reg{I_CB2, MAXCON, R_IN},
+                                 Reg{I_CMASK, MAXCON, 0}};
 };
+// M^-1 is staged (read-only) for the noslip sweeps; the same shared-memory region then holds the (M + hB) factor
 struct MapFinish {
   static constexpr int NT = 20, NI = 2;
   static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),
                                  VR(V_QACC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_QFC, R_IN | R_OUT), VR(V_T1, R_ZERO),
-                                 VR(V_DINV, R_ZERO), Reg{O_H, NTRI, 0}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},
+                                 VR(V_DINV, R_ZERO), Reg{SM_T + G_MINV, NTRI, R_IN}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},
                                  Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}, Reg{O_AV, CROWS, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
                                  Reg{O_CBT, MAXCON * 3, R_IN}, Reg{O_EF, MAXCON * 6, R_IN | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
   static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON, R_IN}};
@@ -225,7 +227,7 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
       T* x = c.template V<V_T1>();
       const T h = m.timestep;
       if (m.any_damping) {
-        T* H = c.template S<O_H>();
+        T* H = c.template G<G_MINV>();   // the staged copy of M^-1 (noslip is done with it) doubles as the factor buffer
         const T* M = c.template S<O_M>();
         const T *qfs = c.template V<V_QFS>();
         for (int p = lane; p < NTRI; p += 32) H[p] = M[p];

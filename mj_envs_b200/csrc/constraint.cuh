@@ -326,12 +326,13 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   const T *sD = c.template S<O_SD>(), *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>();
   T *sforce = c.template S<O_SFORCE>(), *qfc = c.template V<V_QFC>();
   T cost = 0;
+  bool changed = false;   // did any row / pyramid edge move between the quadratic and the inactive (or linear) zone?
   if (want_qfc) {
     for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
     __syncwarp();
   }
   for (int r = c.lane; r < c.nsimple; r += 32) {
-    int info = sinfo[r] & 0x1fff;
+    int info = sinfo[r] & 0x1fff, old_state = (sinfo[r] >> 13) & 1;
     T jar = simple_dot(m, info, qacc) - saref[r], D = sD[r], f;
     int state;
     if ((info & 3) == S_FRICTION) {
@@ -343,6 +344,7 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
     else { f = 0; state = 0; }
     sforce[r] = f;
     sinfo[r] = info | (state << 13);
+    changed |= state != old_state;
     if (want_qfc && f != 0) {
       int kind = info & 3, id = (info >> 2) & 1023, up = (info >> 12) & 1;
       if (kind == S_FRICTION) atomicAdd(qfc + id, f);
@@ -357,9 +359,11 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   // contacts: one lane per contact walks its edges; builds the 4x4 Hessian weight W and the frame force
   const T *ac = c.template S<O_AC>(), *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>();
   T *ef = c.template S<O_EF>(), *W = c.template S<O_W>();
+  int* cmask = c.template I<I_CMASK>();
   for (int ci = c.lane; ci < c.ncon; ci += 32) {
     int dim = c.template I<I_CDIM>()[ci], ne = n_edges<T>(dim);
     T D = cD[ci], w[7] = {0, 0, 0, 0, 0, 0, 0};
+    int emask = 0;
     for (int e = 0; e < ne; e++) {
       T sign;
       int k;
@@ -367,6 +371,7 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
       T jar = val - (carefn[ci] + sign * cbt[3 * ci + k]);
       T f = 0;
       if (jar < 0) {
+        emask |= 1 << e;
         f = -D * jar;
         cost += T(0.5) * D * jar * jar;
         T smu = sign * cmu[3 * ci + k];
@@ -376,7 +381,10 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
       ef[6 * ci + e] = f;
     }
     for (int q = 0; q < 7; q++) W[7 * ci + q] = w[q];
+    changed |= emask != cmask[ci];
+    cmask[ci] = emask;
   }
+  c.nchanged = __any_sync(0xffffffffu, changed);
   __syncwarp();
   if (want_qfc && c.ncon > 0) {
     // frame forces F[ci][4] into O_AV (scratch use), then qfc[j] += sum_r Jr[r][j] F[r]
@@ -404,34 +412,69 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   return warp_sum(cost);
 }
 
-// derivative pair (f', f'') of the constraint cost along qacc + alpha*search
-template <class CX> DI void ls_eval(CX& c, typename CX::real alpha, const typename CX::real* qacc, const typename CX::real* search, typename CX::real& d1, typename CX::real& d2) {
+// Exact line search support.  Along qacc + alpha*search every row's residual is x + alpha*y; x, y and the row
+// constants are computed ONCE per Newton iteration into registers (lane l owns simple rows l, l+32, l+64 and pyramid
+// edges l, l+32, ..., l+160), so that evaluating (f', f'') at a new alpha is pure register arithmetic + two warp sums.
+template <typename T> struct LsRows {
+  T xs[3], ys[3], Ds[3], fs[3], rf[3];   // simple rows: D = 0 marks an absent row, fs < 0 a one-sided (limit) row
+  T xe[6], ye[6], De[6];                 // pyramid edges
+};
+template <class CX> DI void ls_prepare(CX& c, const typename CX::real* qacc, const typename CX::real* search, LsRows<typename CX::real>& R) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
   const int* sinfo = c.template I<I_SINFO>();
   const T *sD = c.template S<O_SD>(), *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>();
-  T a = 0, b = 0;
-  for (int r = c.lane; r < c.nsimple; r += 32) {
-    int info = sinfo[r] & 0x1fff;
-    T x = simple_dot(m, info, qacc) - saref[r], y = simple_dot(m, info, search), D = sD[r], z = x + alpha * y;
-    if ((info & 3) == S_FRICTION) {
-      T fl = sfl[r], rf = fl / D;
-      if (z <= -rf) a += -fl * y;
-      else if (z >= rf) a += fl * y;
-      else { a += D * z * y; b += D * y * y; }
-    } else if (z < 0) { a += D * z * y; b += D * y * y; }
+#pragma unroll
+  for (int q = 0; q < 3; q++) {
+    int r = c.lane + 32 * q;
+    R.Ds[q] = 0; R.xs[q] = 0; R.ys[q] = 0; R.fs[q] = -1; R.rf[q] = 0;
+    if (r < c.nsimple) {
+      int info = sinfo[r] & 0x1fff;
+      T D = sD[r];
+      R.xs[q] = simple_dot(m, info, qacc) - saref[r];
+      R.ys[q] = simple_dot(m, info, search);
+      R.Ds[q] = D;
+      if ((info & 3) == S_FRICTION) { R.fs[q] = sfl[r]; R.rf[q] = sfl[r] / D; }
+    }
   }
-  const T *ac = c.template S<O_AC>(), *av = c.template S<O_AV>(), *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>();
-  for (int t = c.lane; t < 6 * c.ncon; t += 32) {
-    int ci = t / 6, e = t - 6 * ci, dim = c.template I<I_CDIM>()[ci];
-    if (e >= n_edges<T>(dim)) continue;
-    T sign;
-    int k;
-    T x = edge_val(ac + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
-    x -= carefn[ci] + sign * cbt[3 * ci + k];
-    T y = edge_val(av + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
-    T D = cD[ci], z = x + alpha * y;
-    if (z < 0) { a += D * z * y; b += D * y * y; }
+  const T *ac = c.template S<O_AC>(), *av = c.template S<O_AV>(), *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>();
+  const T *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>();
+  const int* cdim = c.template I<I_CDIM>();
+#pragma unroll
+  for (int q = 0; q < 6; q++) {
+    int t = c.lane + 32 * q;
+    R.De[q] = 0; R.xe[q] = 0; R.ye[q] = 0;
+    if (t < 6 * c.ncon) {
+      int ci = t / 6, e = t - 6 * ci, dim = cdim[ci];
+      if (e < n_edges<T>(dim)) {
+        T sign;
+        int k;
+        T x = edge_val(ac + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
+        R.xe[q] = x - (carefn[ci] + sign * cbt[3 * ci + k]);
+        R.ye[q] = edge_val(av + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
+        R.De[q] = cD[ci];
+      }
+    }
+  }
+}
+// derivative pair (f', f'') of the constraint cost at alpha
+template <typename T> DI void ls_eval(const LsRows<T>& R, T alpha, T& d1, T& d2) {
+  T a = 0, b = 0;
+#pragma unroll
+  for (int q = 0; q < 3; q++) {
+    T D = R.Ds[q], y = R.ys[q], z = R.xs[q] + alpha * y;
+    if (D > 0) {
+      if (R.fs[q] >= 0) {
+        if (z <= -R.rf[q]) a += -R.fs[q] * y;
+        else if (z >= R.rf[q]) a += R.fs[q] * y;
+        else { a += D * z * y; b += D * y * y; }
+      } else if (z < 0) { a += D * z * y; b += D * y * y; }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 6; q++) {
+    T D = R.De[q], y = R.ye[q], z = R.xe[q] + alpha * y;
+    if (D > 0 && z < 0) { a += D * z * y; b += D * y * y; }
   }
   d1 = warp_sum(a);
   d2 = warp_sum(b);
@@ -536,6 +579,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
   __syncwarp();
   T cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
   int iters = 0;
+  bool refactor = true;
   for (int iter = 0; iter < m.iterations; iter++) {
     T g2 = 0;
     for (int j = lane; j < nv; j += 32) {
@@ -546,8 +590,10 @@ template <class CX> PHASE_FN void newton(CX& c) {
     }
     g2 = warp_sum(g2);
     if (scale * sqrt(g2) < m.tolerance) break;
-    build_hessian(c);
-    chol_dense(H, c.template V<V_DINV>(), nv, lane);
+    if (refactor) {   // an unchanged active set leaves the Hessian (and its factor) of the previous iteration valid
+      build_hessian(c);
+      chol_dense(H, c.template V<V_DINV>(), nv, lane);
+    }
     chol_solve(H, c.template V<V_DINV>(), search, nv, lane);
     symv(M, search, Mv, nv, lane);
     contact_frame_mul(c, search, av);
@@ -558,7 +604,9 @@ template <class CX> PHASE_FN void newton(CX& c) {
     A0 = warp_sum(A0);
     B0 = warp_sum(B0);
     T d1, d2;
-    ls_eval(c, T(0), qacc, search, d1, d2);
+    LsRows<T> R;
+    ls_prepare(c, qacc, search, R);
+    ls_eval(R, T(0), d1, d2);
     T f1 = B0 + d1, f2 = A0 + d2;
     T alpha = 0;
     if (f1 < 0) {
@@ -566,7 +614,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
       T lo = 0, hi = -1;  // hi < 0: unbounded
       alpha = -f1 / f2;
       for (int it = 0; it < 40; it++) {
-        ls_eval(c, alpha, qacc, search, d1, d2);
+        ls_eval(R, alpha, d1, d2);
         T fa = A0 * alpha + B0 + d1, fb = A0 + d2;
         if (tabs(fa) <= gtol) break;
         if (fa < 0) lo = alpha; else hi = alpha;
@@ -583,6 +631,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     __syncwarp();
     T old = cost;
     cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
+    refactor = c.nchanged != 0;
     iters = iter + 1;
     // fp32: an improvement below the rounding noise of the cost itself (~1e-6 relative) cannot be measured; Newton's
     // quadratic convergence makes the step after such an iteration a no-op, so stop there instead of burning a factorisation

@@ -55,9 +55,9 @@ template <typename T_, class MAP_> struct Ctx {
   int* gib;  // this env's context block (int): [SM_I | GI_TOTAL]
   int* gi;   // = gib + SM_I
   int lane;
-  int ncon, nsimple;
+  int ncon, nsimple, nchanged;
   __device__ Ctx(const DModel<T>& mm, T* sm_, int* smi_, T* gb_, int* gib_, int lane_)
-      : m(mm), sm(sm_), smi(smi_), gb(gb_), gib(gib_), gi(gib_ + SM_I), lane(lane_), ncon(0), nsimple(0) {}
+      : m(mm), sm(sm_), smi(smi_), gb(gb_), gib(gib_), gi(gib_ + SM_I), lane(lane_), ncon(0), nsimple(0), nchanged(1) {}
   template <int O> static constexpr bool in_smem() { return map_soff<MAP>(O) >= 0; }
   template <int O> DI T* S() const {
     constexpr int so = map_soff<MAP>(O);
@@ -73,33 +73,53 @@ template <typename T_, class MAP_> struct Ctx {
   }
 };
 
-// stage the MAP's regions between the context block and shared memory (whole warp, coalesced)
-template <class CX, int I = 0> DI void stage_in(CX& c) {
+// stage the MAP's regions between the context block and shared memory (whole warp, 16-byte chunks; region offsets and
+// lengths are multiples of 16 bytes by construction).  Loads go through cp.async so that every region is in flight at once.
+DI void cp_async16(void* smem_dst, const void* gmem_src) {
+  unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem_src) : "memory");
+}
+DI void cp_async_wait_all() { asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory"); }
+template <class CX, int I = 0> DI void stage_in_issue(CX& c) {
   using MAP = typename CX::MAP;
+  using T = typename CX::real;
+  constexpr int E = 16 / sizeof(T);
   if constexpr (I < MAP::NT) {
     constexpr Reg r = MAP::RT[I];
     constexpr int so = map_soff<MAP>(r.off);
-    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane; j < r.len; j += 32) c.sm[so + j] = c.gb[r.off + j]; }
+    static_assert(r.off % E == 0 && r.len % E == 0, "regions are staged in 16-byte chunks");
+    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane * E; j < r.len; j += 32 * E) cp_async16(c.sm + so + j, c.gb + r.off + j); }
     else if constexpr ((r.flags & R_ZERO) != 0) { for (int j = c.lane; j < r.len; j += 32) c.sm[so + j] = 0; }
-    stage_in<CX, I + 1>(c);
+    stage_in_issue<CX, I + 1>(c);
   } else if constexpr (I < MAP::NT + MAP::NI) {
     constexpr Reg r = MAP::RI[I - MAP::NT];
     constexpr int so = map_ioff<MAP>(r.off);
-    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane; j < r.len; j += 32) c.smi[so + j] = c.gib[r.off + j]; }
-    stage_in<CX, I + 1>(c);
+    static_assert(r.off % 4 == 0 && r.len % 4 == 0, "regions are staged in 16-byte chunks");
+    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane * 4; j < r.len; j += 128) cp_async16(c.smi + so + j, c.gib + r.off + j); }
+    stage_in_issue<CX, I + 1>(c);
   }
+}
+template <class CX> DI void stage_in(CX& c) {
+  stage_in_issue(c);
+  cp_async_wait_all();
 }
 template <class CX, int I = 0> DI void stage_out(CX& c) {
   using MAP = typename CX::MAP;
+  using T = typename CX::real;
+  constexpr int E = 16 / sizeof(T);
   if constexpr (I < MAP::NT) {
     constexpr Reg r = MAP::RT[I];
     constexpr int so = map_soff<MAP>(r.off);
-    if constexpr ((r.flags & R_OUT) != 0) { for (int j = c.lane; j < r.len; j += 32) c.gb[r.off + j] = c.sm[so + j]; }
+    if constexpr ((r.flags & R_OUT) != 0) {
+      for (int j = c.lane * E; j < r.len; j += 32 * E) *reinterpret_cast<int4*>(c.gb + r.off + j) = *reinterpret_cast<const int4*>(c.sm + so + j);
+    }
     stage_out<CX, I + 1>(c);
   } else if constexpr (I < MAP::NT + MAP::NI) {
     constexpr Reg r = MAP::RI[I - MAP::NT];
     constexpr int so = map_ioff<MAP>(r.off);
-    if constexpr ((r.flags & R_OUT) != 0) { for (int j = c.lane; j < r.len; j += 32) c.gib[r.off + j] = c.smi[so + j]; }
+    if constexpr ((r.flags & R_OUT) != 0) {
+      for (int j = c.lane * 4; j < r.len; j += 128) *reinterpret_cast<int4*>(c.gib + r.off + j) = *reinterpret_cast<const int4*>(c.smi + so + j);
+    }
     stage_out<CX, I + 1>(c);
   }
 }

@@ -62,7 +62,8 @@ constexpr int I_SINFO = 0;                      // simple rows: kind | id<<2 | (
 constexpr int I_CDIM = I_SINFO + MAXSIMPLE;
 constexpr int I_CB1 = I_CDIM + MAXCON;
 constexpr int I_CB2 = I_CB1 + MAXCON;
-constexpr int I_SURV = I_CB2 + MAXCON;
+constexpr int I_CMASK = I_CB2 + MAXCON;           // active-edge bit mask of every contact (Newton active-set change detection)
+constexpr int I_SURV = I_CMASK + MAXCON;
 constexpr int SM_I = I_SURV + MAXSURV;
 
 template <typename T> constexpr size_t smem_per_warp() { return SM_T * sizeof(T) + SM_I * sizeof(int); }
