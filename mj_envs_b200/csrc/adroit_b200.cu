@@ -82,7 +82,7 @@ template <typename T> DI bool warp_bad(const T* x, int n, int lane) {
 template <class C> DI void zero_state(C& c) {
   using T = typename C::real;
   T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *warm = c.template V<V_WARM>();
-  for (int j = c.lane; j < NVP; j += 32) { qpos[j] = 0; qvel[j] = 0; warm[j] = 0; }
+  _Pragma("unroll 1") for (int j = c.lane; j < NVP; j += 32) { qpos[j] = 0; qvel[j] = 0; warm[j] = 0; }
   __syncwarp();
 }
 
@@ -130,12 +130,12 @@ __global__ void __launch_bounds__(WPB * 32) smooth_kernel(const __grid_constant_
       st.ep_goal[env] = 0;
     }
     T* ctrl = c.template V<V_CTRL>();
-    for (int j = lane; j < NVP; j += 32) ctrl[j] = 0;
+    _Pragma("unroll 1") for (int j = lane; j < NVP; j += 32) ctrl[j] = 0;
     zero_state(c);
   }
   if (a.action) {   // action map: hammer_v0.py:55-59 (act_mid / act_rng :49-50)
     T* ctrl = c.template V<V_CTRL>();
-    for (int u = lane; u < m.nu; u += 32) {
+    _Pragma("unroll 1") for (int u = lane; u < m.nu; u += 32) {
       T x = tclamp((T)a.action[(size_t)env * m.nu + u], T(-1), T(1));
       T lo = m.act_ctrlrange[2 * u], hi = m.act_ctrlrange[2 * u + 1];
       ctrl[u] = T(0.5) * (lo + hi) + x * T(0.5) * (hi - lo);
@@ -198,14 +198,14 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
     symv(c.template G<G_MINV>(), qfc, u, nv, lane);
     __syncwarp();
     const T* qas = c.template V<V_QAS>();
-    for (int j = lane; j < nv; j += 32) qacc[j] = qas[j] + u[j];
+    _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) qacc[j] = qas[j] + u[j];
     __syncwarp();
   }
   T touch = touch_sensor(c);
   cache_task_frames(c, touch);
   if (a.debug) {
     const T *qfs = c.template V<V_QFS>(), *qas = c.template V<V_QAS>();
-    for (int j = lane; j < nv; j += 32) {
+    _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) {
       c.template G<G_DBG_QFS>()[j] = qfs[j];
       c.template G<G_DBG_QAS>()[j] = qas[j];
       c.template G<G_DBG_QACC>()[j] = qacc[j];
@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
         const T *qfs = c.template V<V_QFS>();
         for (int p = lane; p < NTRI; p += 32) H[p] = M[p];
         __syncwarp();
-        for (int j = lane; j < nv; j += 32) {
+        _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) {
           H[tri(j, j)] += h * m.dof_damping[j];
           x[j] = qfs[j] + qfc[j];
         }
@@ -240,10 +240,10 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
         ltdl_factor(m, H, c.template V<V_DINV>(), lane);
         ltdl_solve(H, c.template V<V_DINV>(), x, nv, lane);
       } else {
-        for (int j = lane; j < nv; j += 32) x[j] = qacc[j];
+        _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) x[j] = qacc[j];
         __syncwarp();
       }
-      for (int j = lane; j < nv; j += 32) {
+      _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) {
         T v = qvel[j] + h * x[j];
         qvel[j] = v;
         qpos[j] += h * v;

@@ -16,7 +16,8 @@
 
 namespace adroit {
 
-template <typename T> DI T impedance(const DModel<T>& m, T pos, T margin) {
+// (noinline: the general-power branch pulls in pow(); one copy instead of four keeps the solve kernel's code small)
+template <typename T> SUB_FN T impedance(const DModel<T>& m, T pos, T margin) {
   T s0 = tclamp(m.solimp[0], T(0.0001), T(0.9999)), s1 = tclamp(m.solimp[1], T(0.0001), T(0.9999)), width = m.solimp[2];
   T mid = tclamp(m.solimp[3], T(0.0001), T(0.9999)), power = m.solimp[4] < 1 ? T(1) : m.solimp[4];
   if (s0 == s1 || width <= T(1e-15)) return T(0.5) * (s0 + s1);
@@ -243,7 +244,7 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
     int b1 = c.template I<I_CB1>()[ci], b2 = c.template I<I_CB2>()[ci], dim = c.template I<I_CDIM>()[ci];
     unsigned long long m1 = m.body_dofmask[b1], m2 = m.body_dofmask[b2];
     T vsum[4] = {0, 0, 0, 0};
-    for (int j = c.lane; j < NVP; j += 32) {
+    _Pragma("unroll 1") for (int j = c.lane; j < NVP; j += 32) {
       T row[4] = {0, 0, 0, 0};
       if (j < m.nv) {
         int sg = (int)((m2 >> j) & 1ull) - (int)((m1 >> j) & 1ull);
@@ -299,11 +300,11 @@ template <typename T> DI T simple_dot(const DModel<T>& m, int info, const T* x) 
   return up ? -s : s;
 }
 // contact-frame products  out[ci][a] = Jf[ci][a] . x   (lanes over rows, dof-major layout -> coalesced)
-template <class CX> DI void contact_frame_mul(CX& c, const typename CX::real* x, typename CX::real* out) {
+template <class CX> SUB_FN void contact_frame_mul(CX& c, const typename CX::real* x, typename CX::real* out) {
   using T = typename CX::real;
   const T* JT = c.template G<G_JT>();
   int nrows = 4 * c.ncon;
-  for (int r = c.lane; r < nrows; r += 32) {
+  _Pragma("unroll 1") for (int r = c.lane; r < nrows; r += 32) {
     T s = 0;
     for (int j = 0; j < c.m.nv; j++) s += JT[j * CROWS + r] * x[j];
     out[r] = s;
@@ -328,10 +329,10 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   T cost = 0;
   bool changed = false;   // did any row / pyramid edge move between the quadratic and the inactive (or linear) zone?
   if (want_qfc) {
-    for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
+    _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
     __syncwarp();
   }
-  for (int r = c.lane; r < c.nsimple; r += 32) {
+  _Pragma("unroll 1") for (int r = c.lane; r < c.nsimple; r += 32) {
     int info = sinfo[r] & 0x1fff, old_state = (sinfo[r] >> 13) & 1;
     T jar = simple_dot(m, info, qacc) - saref[r], D = sD[r], f;
     int state;
@@ -360,7 +361,7 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   const T *ac = c.template S<O_AC>(), *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>();
   T *ef = c.template S<O_EF>(), *W = c.template S<O_W>();
   int* cmask = c.template I<I_CMASK>();
-  for (int ci = c.lane; ci < c.ncon; ci += 32) {
+  _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
     int dim = c.template I<I_CDIM>()[ci], ne = n_edges<T>(dim);
     T D = cD[ci], w[7] = {0, 0, 0, 0, 0, 0, 0};
     int emask = 0;
@@ -389,7 +390,7 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   if (want_qfc && c.ncon > 0) {
     // frame forces F[ci][4] into O_AV (scratch use), then qfc[j] += sum_r Jr[r][j] F[r]
     T* F = c.template S<O_AV>();
-    for (int ci = c.lane; ci < c.ncon; ci += 32) {
+    _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
       int dim = c.template I<I_CDIM>()[ci];
       const T* f = ef + 6 * ci;
       if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
@@ -402,7 +403,7 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
     }
     __syncwarp();
     const T* JR = c.template G<G_JR>();
-    for (int j = c.lane; j < m.nv; j += 32) {
+    _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) {
       T s = 0;
       for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
       qfc[j] += s;
@@ -489,7 +490,7 @@ template <class CX> PHASE_FN void build_hessian(CX& c) {
   __syncwarp();
   const int* sinfo = c.template I<I_SINFO>();
   const T* sD = c.template S<O_SD>();
-  for (int r = c.lane; r < c.nsimple; r += 32) {
+  _Pragma("unroll 1") for (int r = c.lane; r < c.nsimple; r += 32) {
     int info = sinfo[r];
     if (!((info >> 13) & 1)) continue;
     int kind = info & 3, id = (info >> 2) & 1023;
@@ -561,7 +562,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
   // cost at the warm start and at qacc_smooth (Gauss term vanishes there)
   auto gauss = [&](const T* a, const T* Maa) {
     T s = 0;
-    for (int j = lane; j < nv; j += 32) s += T(0.5) * (Maa[j] - qfs[j]) * (a[j] - qas[j]);
+    _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) s += T(0.5) * (Maa[j] - qfs[j]) * (a[j] - qas[j]);
     return warp_sum(s);
   };
   symv(M, warm, Ma, nv, lane);
@@ -572,7 +573,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
   __syncwarp();
   T cost_sm = constraint_update(c, qas, false);
   bool use_ws = cost_ws < cost_sm;
-  for (int j = lane; j < nv; j += 32) qacc[j] = use_ws ? warm[j] : qas[j];
+  _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) qacc[j] = use_ws ? warm[j] : qas[j];
   __syncwarp();
   symv(M, qacc, Ma, nv, lane);
   contact_frame_mul(c, qacc, ac);
@@ -582,7 +583,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
   bool refactor = true;
   for (int iter = 0; iter < m.iterations; iter++) {
     T g2 = 0;
-    for (int j = lane; j < nv; j += 32) {
+    _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) {
       T g = Ma[j] - qfs[j] - qfc[j];
       grad[j] = g;
       search[j] = -g;
@@ -600,7 +601,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     __syncwarp();
     // exact line search on the convex piecewise-quadratic: safeguarded Newton on f'(alpha)
     T A0 = 0, B0 = 0;
-    for (int j = lane; j < nv; j += 32) { A0 += search[j] * Mv[j]; B0 += search[j] * (Ma[j] - qfs[j]); }
+    _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) { A0 += search[j] * Mv[j]; B0 += search[j] * (Ma[j] - qfs[j]); }
     A0 = warp_sum(A0);
     B0 = warp_sum(B0);
     T d1, d2;
@@ -626,8 +627,8 @@ template <class CX> PHASE_FN void newton(CX& c) {
       }
     }
     if (alpha == 0) break;
-    for (int j = lane; j < nv; j += 32) { qacc[j] += alpha * search[j]; Ma[j] += alpha * Mv[j]; }
-    for (int r = lane; r < 4 * c.ncon; r += 32) ac[r] += alpha * av[r];
+    _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) { qacc[j] += alpha * search[j]; Ma[j] += alpha * Mv[j]; }
+    _Pragma("unroll 1") for (int r = lane; r < 4 * c.ncon; r += 32) ac[r] += alpha * av[r];
     __syncwarp();
     T old = cost;
     cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
@@ -659,13 +660,13 @@ template <class CX> PHASE_FN void noslip(CX& c) {
     int dim = c.template I<I_CDIM>()[ci];
     for (int k = 0; k + 2 <= dim && k < 3; k++) {
       const T* Jt = JR + (4 * ci + 1 + k) * NVP;
-      for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
+      _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
       __syncwarp();
       T* Y = YT + (3 * ci + k) * NVP;
       symv(Minv, tmp, Y, nv, lane);
       __syncwarp();
       T dsum = 0;
-      for (int i = lane; i < nv; i += 32) dsum += Y[i] * tmp[i];
+      _Pragma("unroll 1") for (int i = lane; i < nv; i += 32) dsum += Y[i] * tmp[i];
       dsum = warp_sum(dsum);
       if (lane == 0) K1[4 * ci + 1 + k] = 4 * cmu[3 * ci + k] * cmu[3 * ci + k] * dsum;
       __syncwarp();
@@ -684,7 +685,7 @@ template <class CX> PHASE_FN void noslip(CX& c) {
       T f = tclamp(old - res / Aii, -fl, fl), delta = f - old;
       __syncwarp();
       if (delta != 0) {
-        for (int j = lane; j < nv; j += 32) u[j] += delta * sym_get(Minv, j, dj);
+        _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) u[j] += delta * sym_get(Minv, j, dj);
         if (lane == 0) sforce[r] = f;
         improvement -= T(0.5) * delta * delta * Aii + delta * res;
       }
@@ -695,7 +696,7 @@ template <class CX> PHASE_FN void noslip(CX& c) {
       for (int k = 0; k + 2 <= dim && k < 3; k++) {
         const T* Jt = JR + (4 * ci + 1 + k) * NVP;
         T s = 0;
-        for (int j = lane; j < nv; j += 32) s += Jt[j] * (u[j] + qas[j]);
+        _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) s += Jt[j] * (u[j] + qas[j]);
         s = warp_sum(s);
         T mu = cmu[3 * ci + k], g = 2 * mu * s - 2 * cbt[3 * ci + k], k1 = K1[4 * ci + 1 + k];
         T f0 = ef[6 * ci + 2 * k], f1 = ef[6 * ci + 2 * k + 1], mid = T(0.5) * (f0 + f1), yold = T(0.5) * (f0 - f1), y = yold;
@@ -705,7 +706,7 @@ template <class CX> PHASE_FN void noslip(CX& c) {
         __syncwarp();
         if (dy != 0) {
           const T* Y = YT + (3 * ci + k) * NVP;
-          for (int j = lane; j < nv; j += 32) u[j] += 2 * mu * dy * Y[j];
+          _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) u[j] += 2 * mu * dy * Y[j];
           if (lane == 0) { ef[6 * ci + 2 * k] = mid + y; ef[6 * ci + 2 * k + 1] = mid - y; }
           improvement -= T(0.5) * k1 * dy * dy + g * dy;
         }
@@ -726,9 +727,9 @@ template <class CX> PHASE_FN void constraint_force(CX& c) {
   T *qfc = c.template V<V_QFC>(), *F = c.template S<O_AV>();
   const int* sinfo = c.template I<I_SINFO>();
   const T *sforce = c.template S<O_SFORCE>(), *ef = c.template S<O_EF>(), *cmu = c.template S<O_CMU>();
-  for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
+  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
   __syncwarp();
-  for (int r = c.lane; r < c.nsimple; r += 32) {
+  _Pragma("unroll 1") for (int r = c.lane; r < c.nsimple; r += 32) {
     T f = sforce[r];
     if (f == 0) continue;
     int info = sinfo[r], kind = info & 3, id = (info >> 2) & 1023, up = (info >> 12) & 1;
@@ -740,7 +741,7 @@ template <class CX> PHASE_FN void constraint_force(CX& c) {
         if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tendon_coef[2 * id + k]);
       }
   }
-  for (int ci = c.lane; ci < c.ncon; ci += 32) {
+  _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
     int dim = c.template I<I_CDIM>()[ci];
     const T* f = ef + 6 * ci;
     if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
@@ -753,7 +754,7 @@ template <class CX> PHASE_FN void constraint_force(CX& c) {
   }
   __syncwarp();
   const T* JR = c.template G<G_JR>();
-  for (int j = c.lane; j < m.nv; j += 32) {
+  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) {
     T s = 0;
     for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
     qfc[j] += s;
@@ -795,7 +796,7 @@ template <class CX> PHASE_FN typename CX::real touch_sensor(CX& c) {
   int sb = m.site_body[m.touch_site];
   const T *ef = c.template S<O_EF>(), *spos = c.template G<G_SPOS>() + 3 * m.touch_site, *smat = c.template S<O_XMAT>() + 9 * sb;
   T sum = 0;
-  for (int ci = c.lane; ci < c.ncon; ci += 32) {
+  _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
     int b1 = c.template I<I_CB1>()[ci], b2 = c.template I<I_CB2>()[ci], dim = c.template I<I_CDIM>()[ci];
     if (sb != b1 && sb != b2) continue;
     T fn = 0;

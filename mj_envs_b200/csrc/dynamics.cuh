@@ -314,7 +314,7 @@ template <class CX> PHASE_FN void mass_matrix(CX& c) {
   }
   for (int p = c.lane; p < NTRI; p += 32) M[p] = 0;
   __syncwarp();
-  for (int i = c.lane; i < m.nv; i += 32) {
+  _Pragma("unroll 1") for (int i = c.lane; i < m.nv; i += 32) {
     int b = m.dof_body[i];
     const T* O = xpos + 3 * b;
     T S[6], F[6];
@@ -399,7 +399,7 @@ template <class CX> PHASE_FN void rne_bias(CX& c) {
     __syncwarp();
   }
   T* bias = c.template V<V_T1>();
-  for (int j = c.lane; j < m.nv; j += 32) {
+  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) {
     int b = m.dof_body[j];
     T S[6];
     dof_motion(m, xanc, xaxis, j, xpos + 3 * b, S);
@@ -440,6 +440,7 @@ template <typename T> DI void store_vec(T* x, int n, int lane, T x0, T x1) {
 
 // for k = n-1..0: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[k][i] * xk for i < k      (row k of L is contiguous)
 template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+#pragma unroll 2
   for (int k = n - 1; k >= 0; k--) {
     T xs = k < 32 ? x0 : x1;
     if (SCALE) xs *= k < 32 ? d0 : d1;
@@ -453,6 +454,7 @@ template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1
 // for k = 0..n-1: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[i][k] * xk for i > k      (column k of L: one row per lane)
 template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
   const T *r0 = L + rowoff(lane), *r1 = L + rowoff(lane + 32);
+#pragma unroll 2
   for (int k = 0; k < n; k++) {
     T xs = k < 32 ? x0 : x1;
     if (SCALE) xs *= k < 32 ? d0 : d1;
@@ -489,6 +491,7 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, int n, int lane) {
   for (int r = 32; r < n; r++) {
     T* rr = A + rowoff(r);
     T x = rr[lane], dl = dinv[lane];
+#pragma unroll 4
     for (int k = 0; k < 32; k++) {          // L11 y = a
       T yk = __shfl_sync(0xffffffffu, x * dl, k);
       if (lane == k) x = yk;
@@ -624,15 +627,15 @@ template <class CX> PHASE_FN void smooth_dynamics(CX& c, bool need_minv) {
   const DModel<T>& m = c.m;
   const T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *bias = c.template V<V_T1>(), *ctrl = c.template V<V_CTRL>();
   T *qfs = c.template V<V_QFS>(), *qas = c.template V<V_QAS>(), *act = c.template V<V_T2>();
-  for (int j = c.lane; j < m.nv; j += 32) act[j] = 0;
+  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) act[j] = 0;
   __syncwarp();
-  for (int u = c.lane; u < m.nu; u += 32) {
+  _Pragma("unroll 1") for (int u = c.lane; u < m.nu; u += 32) {
     T cu = tclamp(ctrl[u], m.act_ctrlrange[2 * u], m.act_ctrlrange[2 * u + 1]);
     int j = m.act_dof[u];
     act[j] = m.act_gain[u] * cu + m.act_bias[3 * u] + m.act_bias[3 * u + 1] * qpos[j] + m.act_bias[3 * u + 2] * qvel[j];
   }
   __syncwarp();
-  for (int j = c.lane; j < m.nv; j += 32) {
+  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) {
     T f = -m.dof_damping[j] * qvel[j] - bias[j] + act[j];
     qfs[j] = f;
     qas[j] = f;

@@ -153,7 +153,7 @@ template <typename T> DI void write_obs(const DModel<T>& m, const T* qpos, const
 // reward / goal_achieved / done: hammer_v0.py:62-90, door_v0.py:63-85, pen_v0.py:75-102, relocate_v0.py:54-72
 template <typename T> DI void task_reward(const DModel<T>& m, const T* qpos, const T* qvel, const T* tf, int lane, T& reward, int& goal, int& done) {
   T v2 = 0;
-  for (int j = lane; j < m.nv; j += 32) v2 += qvel[j] * qvel[j];
+  _Pragma("unroll 1") for (int j = lane; j < m.nv; j += 32) v2 += qvel[j] * qvel[j];
   v2 = warp_sum(v2);
   T r = 0;
   done = 0;

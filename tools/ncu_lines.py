@@ -23,7 +23,7 @@ for f in set(k[0] for k in lines):
     if not os.path.exists(p): continue
     name = "?"; m = {}
     for i, t in enumerate(open(p), 1):
-        mm = re.match(r"^(?:template <[^>]*>\s*)?(?:__device__|DI|__global__|static|inline)[^;{]*?\b([A-Za-z_0-9]+)\s*\(", t)
+        mm = re.match(r"^(?:template <[^>]*>\s*)?(?:__device__|DI|PHASE_FN|SUB_FN|__global__|static|inline)[^;{]*?\b([A-Za-z_0-9]+)\s*\(", t)
         if mm and not t.startswith(" "): name = mm.group(1)
         m[i] = name
     fmap[f] = m
