@@ -210,6 +210,18 @@ def main():
         res = {"value": world * n_envs * steps / (total_ms * 1e-3), "ms_per_step": total_ms / steps, "launches": launches,
                "kernel_ms": float(ms.mean()), "clocks": clocks, "wall_s": wall, "stats": stats.tolist(), "overflow": overflow.tolist(),
                "nu": env.nu, "obs_dim": env.obs_dim}
+        # per-phase device time of the same workload (CUDA events around every phase-kernel launch, on the launching stream)
+        env.profile(True)
+        psteps = min(steps, 40)
+        for i in range(psteps):
+            if flush is not None:
+                flush.fill_(i & 0xFF)
+            raw_step(warmup + steps + i)
+        pms, pn = env.phase_times()
+        env.profile(False)
+        res["phase_ms_per_launch"] = (pms / (psteps * env.frame_skip)).tolist()   # the masked reset pass (a few us) is folded in
+        res["phase_share"] = (pms / pms.sum()).tolist()
+        res["frame_skip"] = env.frame_skip
         if with_e2e:
             # end to end through the reference-facing call: pinned HOST buffers, H2D action + D2H obs/reward/done/goal every step
             a_h = [torch.empty((n_envs, env.nu), dtype=torch.float32).pin_memory() for _ in range(2)]
@@ -250,7 +262,12 @@ def main():
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    achieved = ALGO_BYTES[env_id] * n_envs / (r["kernel_ms"] * 1e-3) / 1e9
+    # dominant kernel: one launch advances n_envs by one physics substep = 1/frame_skip of an env-step
+    names = ["smooth_kernel", "collide_kernel", "solve_kernel", "finish_kernel"]
+    dom = int(np.argmax(r["phase_ms_per_launch"]))
+    bytes_per_launch = ALGO_BYTES[env_id] * n_envs / r["frame_skip"]
+    achieved = bytes_per_launch / (r["phase_ms_per_launch"][dom] * 1e-3) / 1e9
+    step_achieved = ALGO_BYTES[env_id] * n_envs / (r["kernel_ms"] * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -263,6 +280,9 @@ def main():
         "e2e": r["e2e"], "gpu_launches": r["launches"], "clocks": r["clocks"],
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                      "peak_source": peak_src, "algorithmic_bytes_per_env_step": ALGO_BYTES[env_id],
+                     "kernel": names[dom], "kernel_ms_per_launch": r["phase_ms_per_launch"][dom], "algorithmic_bytes_per_launch": bytes_per_launch,
+                     "kernel_share_of_step": r["phase_share"][dom], "phase_ms_per_launch": dict(zip(names, r["phase_ms_per_launch"])),
+                     "whole_step_achieved": step_achieved, "whole_step_frac": step_achieved / peak,
                      "note": "the path is FP32-issue/latency bound, not HBM bound (DESIGN.md §5); reported as mandated"},
         "episode_stats": {"sum_return": r["stats"][0], "episodes_any_goal": r["stats"][1], "episodes_success": r["stats"][2],
                           "episodes": r["stats"][3]},

@@ -99,6 +99,13 @@ int adroit_reduce_episode(adroit_sim* sim, int flush_running, double* out4_host,
 /* Number of kernel launches this handle has enqueued so far (bench.py's gpu_launches). */
 int64_t adroit_launch_count(const adroit_sim* sim);
 
+/* Per-phase device timing (bench.py's roofline: duration of the dominant kernel measured with CUDA events on the
+ * launching stream).  adroit_profile(sim, 1) starts recording an event pair around every phase-kernel launch,
+ * adroit_profile(sim, 0) stops.  adroit_phase_times synchronises the stream and returns, accumulated since the last
+ * call, ms4 = device time of {smooth, collide, solve, finish} kernels and n4 = their launch counts, then clears them. */
+int adroit_profile(adroit_sim* sim, int enable);
+int adroit_phase_times(adroit_sim* sim, double* ms4_host, int64_t* n4_host, void* stream);
+
 /* Counters of capacity overflows since creation: out[0] = contacts dropped (per-env contact buffer full),
  * out[1] = constraint rows dropped.  Both must stay 0 for results to be valid. */
 int adroit_overflow(adroit_sim* sim, int64_t* out2_host, void* stream);

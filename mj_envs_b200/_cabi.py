@@ -24,6 +24,8 @@ SYMBOLS = {
     "reduce_episode": (C.c_int, [_VP, C.c_int, _VP, _VP]),
     "launch_count": (C.c_int64, [_VP]),
     "overflow": (C.c_int, [_VP, _VP, _VP]),
+    "profile": (C.c_int, [_VP, C.c_int]),
+    "phase_times": (C.c_int, [_VP, _VP, _VP, _VP]),
 }
 
 F64, AUTO_RESET, RESET_ON_DONE = 1, 2, 4

@@ -55,7 +55,8 @@ struct MapSolve {
   static constexpr int NT = 24, NI = 5;
   static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_MA, R_ZERO),
                                  VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_QFC, R_ZERO | R_OUT), VR(V_DINV, R_ZERO),
-                                 Reg{O_M, NTRI, R_IN}, Reg{O_H, NTRI, 0},
+                                 Reg{O_M, NTRI, R_IN},   // (A/B: reading M from L1/L2 instead costs 30 %)
+                                 Reg{O_H, NTRI, 0},
                                  Reg{O_SD, MAXSIMPLE, R_OUT}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
                                  Reg{O_AC, CROWS, 0}, Reg{O_AV, CROWS, 0}, Reg{O_CD, MAXCON, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
                                  Reg{O_CAREFN, MAXCON, 0}, Reg{O_CBT, MAXCON * 3, R_OUT}, Reg{O_EF, MAXCON * 6, R_OUT}, Reg{O_W, MAXCON * 7, 0}};
@@ -403,6 +404,8 @@ struct adroit_sim {
   uint8_t *d_done = nullptr, *d_goal = nullptr;
   double* d_out4 = nullptr;
   int64_t launches = 0;
+  bool profile = false;
+  std::vector<cudaEvent_t> prof_ev[4];   // event pairs per phase, pending accumulation
 };
 
 namespace {
@@ -563,11 +566,22 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
 }
 
 template <typename T, class MAP, typename K>
-int launch_phase(adroit_sim* s, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {
+int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {
   size_t smem = WPB * map_bytes<T, MAP>();
   int blocks = (st.n + WPB - 1) / WPB;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (s->profile) {
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, stream));
+  }
   kernel<<<blocks, WPB * 32, smem, stream>>>(m, st, a);
   CK(cudaGetLastError());
+  if (s->profile) {
+    CK(cudaEventRecord(e1, stream));
+    s->prof_ev[phase].push_back(e0);
+    s->prof_ev[phase].push_back(e1);
+  }
   s->launches++;
   return 0;
 }
@@ -582,10 +596,10 @@ template <typename T> int configure_kernels() {
 
 // one mj_forward (+ optional Euler / task epilogue) over the envs selected by a.mask: the four phase kernels in order
 template <typename T> int forward_pass(adroit_sim* s, const DModel<T>& m, const DState<T>& st, PArgs a, cudaStream_t stream) {
-  if (launch_phase<T, MapSmooth>(s, smooth_kernel<T>, m, st, a, stream)) return 1;
-  if (launch_phase<T, MapCollide>(s, collide_kernel<T>, m, st, a, stream)) return 1;
-  if (launch_phase<T, MapSolve>(s, solve_kernel<T>, m, st, a, stream)) return 1;
-  if (launch_phase<T, MapFinish>(s, finish_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapSmooth>(s, 0, smooth_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapCollide>(s, 1, collide_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapSolve>(s, 2, solve_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapFinish>(s, 3, finish_kernel<T>, m, st, a, stream)) return 1;
   return 0;
 }
 
@@ -721,6 +735,7 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
 void adroit_destroy(adroit_sim* s) {
   if (!s) return;
   cudaSetDevice(s->device);
+  for (auto& v : s->prof_ev) for (cudaEvent_t e : v) cudaEventDestroy(e);
   for (void* p : s->allocs) cudaFree(p);
   if (s->stage) cudaFree(s->stage);
   if (s->d_action) cudaFree(s->d_action);
@@ -857,6 +872,30 @@ int adroit_reduce_episode(adroit_sim* s, int flush_running, double* out4_host, v
 }
 
 int64_t adroit_launch_count(const adroit_sim* s) { return s->launches; }
+
+int adroit_profile(adroit_sim* s, int enable) {
+  s->profile = enable != 0;
+  return 0;
+}
+int adroit_phase_times(adroit_sim* s, double* ms4, int64_t* n4, void* stream) {
+  CK(cudaSetDevice(s->device));
+  CK(cudaStreamSynchronize((cudaStream_t)stream));
+  for (int p = 0; p < 4; p++) {
+    double acc = 0;
+    auto& v = s->prof_ev[p];
+    for (size_t i = 0; i + 1 < v.size(); i += 2) {
+      float ms = 0;
+      CK(cudaEventElapsedTime(&ms, v[i], v[i + 1]));
+      acc += ms;
+      cudaEventDestroy(v[i]);
+      cudaEventDestroy(v[i + 1]);
+    }
+    if (ms4) ms4[p] = acc;
+    if (n4) n4[p] = (int64_t)(v.size() / 2);
+    v.clear();
+  }
+  return 0;
+}
 
 int adroit_overflow(adroit_sim* s, int64_t* out2_host, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;

@@ -549,6 +549,9 @@ template <class CX> PHASE_FN void build_hessian(CX& c) {
   }
 }
 
+#ifndef ADROIT_LOCKSTEP
+#define ADROIT_LOCKSTEP 0
+#endif
 // ---------------------------------------------------------------- Newton solver (primal, exact line search)
 template <class CX> PHASE_FN void newton(CX& c) {
   using T = typename CX::real;
@@ -581,7 +584,17 @@ template <class CX> PHASE_FN void newton(CX& c) {
   T cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
   int iters = 0;
   bool refactor = true;
+  bool done = false;
   for (int iter = 0; iter < m.iterations; iter++) {
+#if ADROIT_LOCKSTEP
+    // the warps of a block enter every Newton iteration together: one instruction-cache working set per block
+    if (!__syncthreads_or(!done)) break;
+    if (done) continue;
+#else
+    if (done) break;
+#endif
+    done = true;   // cleared at the end of a full iteration; every early exit below leaves it set
+    do {
     T g2 = 0;
     _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) {
       T g = Ma[j] - qfs[j] - qfc[j];
@@ -638,6 +651,8 @@ template <class CX> PHASE_FN void newton(CX& c) {
     // quadratic convergence makes the step after such an iteration a no-op, so stop there instead of burning a factorisation
     T floor_ = sizeof(T) == 4 ? T(2e-6) * tabs(cost) : T(0);
     if (scale * (old - cost) < m.tolerance || (old - cost) < floor_) break;
+    done = false;
+    } while (0);
   }
   if (lane == 0) c.gi[GI_NITER] = iters;
 }

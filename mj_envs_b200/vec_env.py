@@ -223,6 +223,15 @@ class AdroitVecEnv:
         self.abi.check(self.abi.overflow(self._h, o.ctypes.data, self._stream()))
         return o
 
+    def profile(self, enable=True):
+        self.abi.check(self.abi.profile(self._h, int(enable)))
+
+    def phase_times(self):
+        """(ms[4], launches[4]) of the smooth / collide / solve / finish kernels since the last call (needs profile(True))."""
+        ms, n = np.zeros(4), np.zeros(4, dtype=np.int64)
+        self.abi.check(self.abi.phase_times(self._h, ms.ctypes.data, n.ctypes.data, self._stream()))
+        return ms, n
+
     def launch_count(self):
         return int(self.abi.launch_count(self._h))
 
