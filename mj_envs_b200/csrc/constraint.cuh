@@ -57,6 +57,16 @@ template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow)
   using T = typename CX::real;
   const DModel<T>& m = c.m;
   const T *gpos = c.template G<G_GPOS>(), *gmat = c.template G<G_GMAT>();
+  // hammer "size" variation (hammer_v0.py:123-125): geom_size of the head is a per-env parameter; geom_rbound stays stale
+  // as in MuJoCo (the model is not recompiled), except in this file's own extra culls, which must stay conservative
+  const int var_geom = m.task_int[8] == VAR_SIZE ? m.task_int[10] : -1;
+  const T *par = c.template S<O_PAR>();
+  auto gsize = [&](int g, int k) -> T { return (g == var_geom && k < 2) ? par[3 + k] : m.geom_size[3 * g + k]; };
+  auto rb_safe = [&](int g) -> T {
+    T rb = m.geom_rbound[g];
+    if (g == var_geom) rb = tmax(rb, sqrt(par[3] * par[3] + par[4] * par[4]));
+    return rb;
+  };
   int* surv = c.template I<I_SURV>();
   const unsigned lt = (1u << c.lane) - 1u;
   int nsurv = 0;
@@ -75,8 +85,9 @@ template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow)
         hit = !(dx * dx + dy * dy + dz * dz > bound * bound);
         // second, tighter (still conservative) test: the other geom's bounding sphere against this geom's own shape
         // (large boxes -- table, wall, door -- have bounding spheres that swallow the whole hand)
-        if (hit) hit = !(shape_lower_bound(m.geom_type[g1], gmat + 9 * g1, m.geom_size + 3 * g1, dx, dy, dz) > m.geom_rbound[g2] + margin);
-        if (hit) hit = !(shape_lower_bound(m.geom_type[g2], gmat + 9 * g2, m.geom_size + 3 * g2, -dx, -dy, -dz) > m.geom_rbound[g1] + margin);
+        T z1[3] = {gsize(g1, 0), gsize(g1, 1), gsize(g1, 2)}, z2[3] = {gsize(g2, 0), gsize(g2, 1), gsize(g2, 2)};
+        if (hit) hit = !(shape_lower_bound(m.geom_type[g1], gmat + 9 * g1, z1, dx, dy, dz) > rb_safe(g2) + margin);
+        if (hit) hit = !(shape_lower_bound(m.geom_type[g2], gmat + 9 * g2, z2, -dx, -dy, -dz) > rb_safe(g1) + margin);
       }
     }
     unsigned mask = __ballot_sync(0xffffffffu, hit);
@@ -106,8 +117,8 @@ template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow)
       for (int e = 0; e < 9; e++) { R1.m[e] = gmat[9 * g1 + e]; R2.m[e] = gmat[9 * g2 + e]; }
       origin = mk<T>(gpos[3 * g1], gpos[3 * g1 + 1], gpos[3 * g1 + 2]);
       V3<T> p2 = mk<T>(gpos[3 * g2], gpos[3 * g2 + 1], gpos[3 * g2 + 2]) - origin;
-      V3<T> s1 = mk<T>(m.geom_size[3 * g1], m.geom_size[3 * g1 + 1], m.geom_size[3 * g1 + 2]);
-      V3<T> s2 = mk<T>(m.geom_size[3 * g2], m.geom_size[3 * g2 + 1], m.geom_size[3 * g2 + 2]);
+      V3<T> s1 = mk<T>(gsize(g1, 0), gsize(g1, 1), gsize(g1, 2));
+      V3<T> s2 = mk<T>(gsize(g2, 0), gsize(g2, 1), gsize(g2, 2));
       collide_pair(out, m.pair_margin[k], m.geom_type[g1], mk<T>(0, 0, 0), R1, s1, m.geom_type[g2], p2, R2, s2,
                    m.mpr_iterations, m.mpr_tolerance);
     }

@@ -219,7 +219,12 @@ template <class CX> PHASE_FN void frames_and_inertia(CX& c) {
   for (int g = c.lane; g < m.ngeom; g += 32) {
     int b = m.geom_body[g];
     T t[3];
-    rot(t, xmat + 9 * b, m.geom_pos + 3 * g);
+    T gp[3] = {m.geom_pos[3 * g], m.geom_pos[3 * g + 1], m.geom_pos[3 * g + 2]};
+    if (m.task_int[8] == VAR_POS) {   // hammer "pos" variation (hammer_v0.py:119-122): head / neck slide along the handle
+      if (g == m.task_int[10]) gp[0] = par[3];
+      if (g == m.task_int[11]) gp[0] = par[4];
+    }
+    rot(t, xmat + 9 * b, gp);
     for (int i = 0; i < 3; i++) c.template G<G_GPOS>()[3 * g + i] = xpos[3 * b + i] + t[i];
     const T *A = xmat + 9 * b, *B = m.geom_mat + 9 * g;
     for (int i = 0; i < 3; i++)
@@ -235,7 +240,7 @@ template <class CX> PHASE_FN void frames_and_inertia(CX& c) {
   // inertia {m, h[3] = m*c, I[6] = xx,yy,zz,xy,xz,yz} about xpos[b], world axes
   T* crb = c.template S<O_CRB>();
   for (int b = c.lane; b < m.nbody; b += 32) {
-    T mass = m.body_mass[b], Rw[9], cv[3];
+    T mass = (m.task_int[8] == VAR_MASS && b == m.task_int[9]) ? par[3] : m.body_mass[b], Rw[9], cv[3];   // hammer_v0.py:115-118
     const T *A = xmat + 9 * b, *B = m.body_imat + 9 * b, *dg = m.body_inertia + 3 * b;
     for (int i = 0; i < 3; i++)
       for (int j = 0; j < 3; j++) Rw[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];

@@ -27,6 +27,9 @@ constexpr int MAXSURV = 96;    // candidate pairs surviving the bounding-sphere 
 
 enum { T_HAMMER = 0, T_DOOR = 1, T_PEN = 2, T_RELOCATE = 3 };
 enum { J_SLIDE = 2, J_HINGE = 3 };
+// hammer variation types (hammer_v0.py:110-129); task_int[8] = type, [9] = Object body, [10] = head geom, [11] = neck geom;
+// the drawn values live in the per-env parameters par[3], par[4]
+enum { VAR_NONE = 0, VAR_MASS = 1, VAR_POS = 2, VAR_SIZE = 3 };
 enum { S_FRICTION = 0, S_JLIMIT = 1, S_TLIMIT = 2 };
 
 // ---- shared memory (per warp), offsets in units of T

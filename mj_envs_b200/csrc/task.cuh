@@ -26,7 +26,22 @@ template <typename T> DI void draw_params(const DModel<T>& m, unsigned long long
   philox4x32((unsigned)seed, (unsigned)(seed >> 32), (unsigned)genv, (unsigned)(genv >> 32), episode, 1, r + 4);
   for (int i = 0; i < m.npar; i++) par[i] = m.par0[i];
   switch (m.task) {
-    case T_HAMMER: par[2] = (T)(0.1 + u01(r[0]) * (0.25 - 0.1)); break;
+    case T_HAMMER:
+      par[2] = (T)(0.1 + u01(r[0]) * (0.25 - 0.1));
+      switch (m.task_int[8]) {   // variations, hammer_v0.py:115-125 (drawn after the board height, same order)
+        case VAR_MASS: par[3] = (T)(0.05 + u01(r[1]) * (2.5 - 0.05)); break;
+        case VAR_POS: {
+          double x = -0.24 + u01(r[1]) * (-0.10 + 0.24);
+          par[3] = (T)x;
+          par[4] = (T)(-0.14 - (-0.24 - x));
+        } break;
+        case VAR_SIZE:
+          par[3] = (T)(0.01 + u01(r[1]) * (0.04 - 0.01));
+          par[4] = (T)(0.02 + u01(r[2]) * (0.08 - 0.02));
+          break;
+        default: break;
+      }
+      break;
     case T_DOOR:
       par[0] = (T)(-0.3 + u01(r[0]) * 0.1);
       par[1] = (T)(0.25 + u01(r[1]) * 0.1);

@@ -112,6 +112,29 @@ class Model:
     def name2id(self, kind, name):
         return self.names[kind].index(name)
 
+    def with_variation(self, variation_type):
+        """Copy of a hammer scene whose reset draws the reference's `variation_type` (hammer_v0.py:110-129):
+        'mass' (body_mass[Object] ~ U(0.05, 2.5)), 'pos' (geom_pos x of head / neck), 'size' (geom_size[head][0:2]).
+        The drawn values become per-env parameters par[3], par[4]; nothing is recompiled (inertia tensor,
+        invweight0 and geom_rbound stay stale, as in the reference -- SURVEY.md App. A.8 Q9)."""
+        codes = {"mass": 1, "pos": 2, "size": 3}
+        if variation_type not in codes or self.task != "hammer":
+            raise Exception(f"Unsupported variation type {variation_type}")   # hammer_v0.py:129
+        A = {k: v.copy() for k, v in self.A.items()}
+        head, neck, obj = self.name2id("geom", "head"), self.name2id("geom", "neck"), self.name2id("body", "Object")
+        A["task_int"][8:12] = [codes[variation_type], obj, head, neck]
+        par0 = np.zeros(5)
+        par0[:3] = A["par0"][:3]
+        if variation_type == "mass":
+            par0[3] = A["body_mass"][obj]
+        elif variation_type == "pos":
+            par0[3], par0[4] = A["geom_pos"].reshape(-1, 3)[head, 0], A["geom_pos"].reshape(-1, 3)[neck, 0]
+        else:
+            par0[3], par0[4] = A["geom_size"].reshape(-1, 3)[head, 0], A["geom_size"].reshape(-1, 3)[head, 1]
+        A["par0"] = par0
+        A["sizes"][7] = 5
+        return Model(task=self.task, names=self.names, A=A)
+
     # sizes
     @property
     def nv(self): return int(self.A["sizes"][0])
@@ -194,7 +217,8 @@ _SHAPES = {"body_pos": 3, "body_quat": 4, "body_ipos": 3, "body_iquat": 4, "body
            "jnt_pos": 3, "jnt_axis": 3, "jnt_range": 2, "geom_pos": 3, "geom_quat": 4, "geom_size": 3,
            "geom_friction": 3, "site_pos": 3, "site_quat": 4, "site_size": 3, "act_ctrlrange": 2,
            "tendon_range": 2, "tendon_dof": 2, "tendon_coef": 2, "pair_geom": 2, "pair_friction": 5,
-           "body_invweight0": 2, "body_par": 2, "act_bias": 3, "geom_rgba": 4, "cam_pos": 3, "cam_quat": 4, "light_pos": 3}
+           "body_invweight0": 2, "body_par": 2, "act_bias": 3, "geom_rgba": 4, "cam_pos": 3, "cam_quat": 4, "light_pos": 3,
+           "render_int": 4, "render_real": 19, "light_diffuse": 3}
 
 
 def _encode_names(task, names):
@@ -298,6 +322,7 @@ def load_mjcf(path: str, task: str | None = None) -> Model:
     bodies, joints, geoms, sites, cams, lights = [], [], [], [], [], []
     pairs_x, excludes, tendons, actuators, sensors = [], [], [], [], []
     materials = {}
+    textures = {}
 
     bodies.append(dict(name="world", parent=-1, pos=np.zeros(3), quat=np.array([1.0, 0, 0, 0]),
                        inertial=None, mocap=False))
@@ -346,12 +371,14 @@ def load_mjcf(path: str, task: str | None = None) -> Model:
                 a = dfl.resolve("site", ch.attrib)
                 sites.append(dict(name=a.get("name", f"site{len(sites)}"), body=bid,
                                   type=a.get("type", "sphere"), pos=_vec(a.get("pos"), 3, [0, 0, 0]),
-                                  quat=_orient(a), size=_vec(a.get("size"), 3, [0.005, 0, 0])))
+                                  quat=_orient(a), size=_vec(a.get("size"), 3, [0.005, 0, 0]),
+                                  rgba=_vec(a.get("rgba"), 4, [0.5, 0.5, 0.5, 1.0]), group=int(a.get("group", 0))))
             elif ch.tag == "camera":
                 cams.append(dict(name=ch.attrib.get("name", ""), body=bid,
                                  pos=_vec(ch.attrib.get("pos"), 3, [0, 0, 0]), quat=_orient(ch.attrib)))
             elif ch.tag == "light":
-                lights.append(dict(pos=_vec(ch.attrib.get("pos"), 3, [0, 0, 0])))
+                lights.append(dict(pos=_vec(ch.attrib.get("pos"), 3, [0, 0, 0]), body=bid,
+                                   diffuse=_vec(ch.attrib.get("diffuse"), 3, [0.7, 0.7, 0.7])))
 
     # document order matters for defaults (copy-at-creation), so walk top-level sequentially
     for sec in root:
@@ -366,8 +393,14 @@ def load_mjcf(path: str, task: str | None = None) -> Model:
                     opt[k] = int(sec.attrib[k])
         elif sec.tag == "asset":
             for ch in sec:
+                if ch.tag == "texture" and ch.attrib.get("builtin", "none") != "none":
+                    r1, r2 = _vec(ch.attrib.get("rgb1"), 3, [0.8, 0.8, 0.8]), _vec(ch.attrib.get("rgb2"), 3, [0.5, 0.5, 0.5])
+                    textures[ch.attrib.get("name", "")] = r1 if ch.attrib["builtin"] == "flat" else 0.5 * (r1 + r2)
                 if ch.tag == "material":
-                    materials[ch.attrib["name"]] = _vec(ch.attrib.get("rgba"), 4, [1, 1, 1, 1])
+                    rgba = _vec(ch.attrib.get("rgba"), 4, [1, 1, 1, 1]).copy()
+                    if ch.attrib.get("texture") in textures:   # builtin texture: its mean colour stands in (no GL here)
+                        rgba[:3] *= textures[ch.attrib["texture"]]
+                    materials[ch.attrib["name"]] = rgba
     # MuJoCo resolves element defaults when the element is parsed; worldbody appears before the
     # included defaults file in the task XMLs, but MuJoCo's parser handles <default> sections first
     # within one file pass of each top-level section type.  All body elements in these scenes use
@@ -669,6 +702,35 @@ def _compile(task, opt, bodies, joints, geoms_all, sites, cams, lights, pairs_x,
             touch_site = sid(s["site"])
     A["touch_site"] = np.array([touch_site], dtype=np.int32)
 
+    # ---- render table for the pixel path (reference headless_observer.py).  Meshes and texture
+    # files are absent and no GL exists here, so the CUDA ray-caster draws every primitive geom (collision shapes
+    # included: they stand in for the missing visual meshes) and the visible sites (group <= 2; translucent ones are alpha-blended) with
+    # their material colours.  render_int rows: type, body, per-env parameter offset of the local position (-1 = none),
+    # is_site; render_real rows: local pos[3], local mat[9], size[3], rgba[4].
+    rg_int, rg_real = [], []
+    rg_of_geom = {}
+    for g in geoms_all:
+        if g["rgba"][3] <= 0.0:
+            continue
+        rg_of_geom[id(g)] = len(rg_int)
+        rg_int.append([g["type"], g["body"], -1, 0])
+        rg_real.append(np.concatenate([g["pos"], quat_to_mat(g["quat"]).ravel(), g["size"], g["rgba"][:3], [1.0]]))   # geoms are drawn opaque
+    for si, st in enumerate(sites):
+        if st["group"] > 2 or st["rgba"][3] < 0.05:
+            continue
+        ty = {"sphere": GEOM_SPHERE, "box": GEOM_BOX, "cylinder": GEOM_CYLINDER}[st["type"]]
+        rg_int.append([ty, st["body"], int(site_par[si]), 1])
+        rg_real.append(np.concatenate([st["pos"], quat_to_mat(st["quat"]).ravel(), st["size"], st["rgba"]]))           # sites keep their alpha
+    A["render_int"] = np.array(rg_int, dtype=np.int32).reshape(-1, 4)
+    A["render_real"] = np.array(rg_real).reshape(-1, 19)
+    A["render_geom_index"] = np.array([rg_of_geom.get(id(g), -1) for g in keep], dtype=np.int32)   # collidable geom -> render row
+    A["light_diffuse"] = np.array([l["diffuse"] for l in lights]).reshape(-1, 3)
+    A["light_body"] = np.array([l["body"] for l in lights], dtype=np.int32)
+    A["cam_body"] = np.array([c["body"] for c in cams], dtype=np.int32)
+    # which body the reference hands to HeadlessObserver: hammer -1 (= last body), door / relocate the
+    # placeholder 0 (door_v0.py:41, relocate_v0.py:32), pen its own setup with the target body (pen_v0.py:163-177)
+    A["render_obj_body"] = np.array([{"hammer": nb - 1, "door": 0, "relocate": 0, "pen": bid("target") if task == "pen" else 0}[task]],
+                                    dtype=np.int32)
     A["sizes"] = np.array([nv, nb, ng, len(sites), nu, nt, len(pair_rows), npar, obs_dim, frame_skip,
                            TASK_IDS[task], horizon, n_dynamic, len(cams), 0, 0], dtype=np.int32)
 

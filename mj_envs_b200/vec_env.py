@@ -65,14 +65,17 @@ class AdroitVecEnv:
                  env_id_offset: int = 0, frame_skip: int | None = None, model: Model | None = None):
         if env_id not in ENV_IDS:
             raise ValueError(f"unknown env id {env_id!r}; expected one of {sorted(ENV_IDS)}")
-        if variation_type is not None:
-            raise Exception(f"Unsupported variation type {variation_type}")  # hammer_v0.py:129 (variations: SURVEY §8f N2)
         if not torch.cuda.is_available():
             raise RuntimeError("AdroitVecEnv needs a CUDA device (no CPU fallback)")
         self.env_id = env_id
         self.device = torch.device(device if not isinstance(device, int) else f"cuda:{device}")
         self.num_envs = int(num_envs)
         self.model = model if model is not None else load_compiled(ENV_IDS[env_id])
+        # variation_type: only HammerEnvV0 acts on it (hammer_v0.py:110-129); door/pen/relocate store and ignore it
+        # (door_v0.py:29, pen_v0.py:32, relocate_v0.py:22)
+        self.variation_type = variation_type
+        if variation_type is not None and env_id == "hammer-v0":
+            self.model = self.model.with_variation(variation_type)
         if frame_skip is not None:
             self.model.A["sizes"] = self.model.A["sizes"].copy()
             self.model.A["sizes"][9] = frame_skip

@@ -37,6 +37,8 @@
 enum { G_PLANE = 0, G_SPHERE = 2, G_CAPSULE = 3, G_CYLINDER = 5, G_BOX = 6 };
 enum { J_SLIDE = 2, J_HINGE = 3 };
 enum { T_HAMMER = 0, T_DOOR = 1, T_PEN = 2, T_RELOCATE = 3 };
+/* hammer variations (hammer_v0.py:110-129): task_int[8] = type, [9] = Object body, [10] = head geom, [11] = neck geom; values in par[3], par[4] */
+enum { VAR_NONE = 0, VAR_MASS = 1, VAR_POS = 2, VAR_SIZE = 3 };
 enum { C_FRICTION = 0, C_LIMIT_JOINT = 1, C_LIMIT_TENDON = 2, C_CONTACT_FRICTIONLESS = 3, C_CONTACT_PYRAMIDAL = 4 };
 
 static __thread char g_err[256];
@@ -212,6 +214,7 @@ typedef struct {
   OContact con[MAXCON];
   double touch;
   int solver_iter;
+  double var_size[3];
 } OData;
 
 /* solver workspace (per thread) */
@@ -234,6 +237,19 @@ typedef struct {
 } OSim;
 
 /* ------------------------------------------------------------------ kinematics */
+/* per-env overrides of model fields written by the hammer variations (the model is NOT recompiled: inertia tensor,
+   invweight0 and geom_rbound stay stale, hammer_v0.py:115-125 / SURVEY.md App. A.8 Q9) */
+static double body_mass_of(const OModel* m, const OData* d, int b) {
+  return (m->task_int[8] == VAR_MASS && b == m->task_int[9]) ? d->par[3] : m->body_mass[b];
+}
+static const double* geom_size_of(const OModel* m, OData* d, int g) {
+  if (m->task_int[8] == VAR_SIZE && g == m->task_int[10]) {
+    d->var_size[0] = d->par[3]; d->var_size[1] = d->par[4]; d->var_size[2] = m->geom_size[3 * g + 2];
+    return d->var_size;
+  }
+  return m->geom_size + 3 * g;
+}
+
 static void o_kinematics(const OModel* m, OData* d) {
   memset(d->xpos[0], 0, sizeof d->xpos[0]);
   d->xquat[0][0] = 1; d->xquat[0][1] = d->xquat[0][2] = d->xquat[0][3] = 0;
@@ -278,7 +294,12 @@ static void o_kinematics(const OModel* m, OData* d) {
   for (int g = 0; g < m->ngeom; g++) {
     int b = m->geom_body[g];
     double t[3], R[9];
-    mulMV(t, d->xmat[b], m->geom_pos + 3 * g);
+    double gp[3] = {m->geom_pos[3 * g], m->geom_pos[3 * g + 1], m->geom_pos[3 * g + 2]};
+    if (m->task_int[8] == VAR_POS) {   /* hammer_v0.py:119-122 */
+      if (g == m->task_int[10]) gp[0] = d->par[3];
+      if (g == m->task_int[11]) gp[0] = d->par[4];
+    }
+    mulMV(t, d->xmat[b], gp);
     add3(d->gpos[g], d->xpos[b], t);
     quat2mat(R, m->geom_quat + 4 * g);
     mulMM(d->gmat[g], d->xmat[b], R);
@@ -378,7 +399,7 @@ static void chol_solve(int n, double L[MAXV][MAXV], double* x) {
 static void o_mass_matrix(const OModel* m, OData* d) {
   SpI crb[MAXB];
   int nv = m->nv;
-  for (int b = 0; b < m->nbody; b++) spi_body(&crb[b], m->body_mass[b], d->xipos[b], d->ximat[b], m->body_inertia + 3 * b);
+  for (int b = 0; b < m->nbody; b++) spi_body(&crb[b], body_mass_of(m, d, b), d->xipos[b], d->ximat[b], m->body_inertia + 3 * b);
   for (int b = m->nbody - 1; b > 0; b--) spi_add(&crb[m->body_parent[b]], &crb[b]);
   for (int i = 0; i < nv; i++)
     for (int j = 0; j < nv; j++) d->M[i][j] = 0;
@@ -419,7 +440,7 @@ static void o_bias(const OModel* m, OData* d) {
     memcpy(vel[b], v, sizeof v);
     memcpy(acc[b], a, sizeof a);
     SpI I;
-    spi_body(&I, m->body_mass[b], d->xipos[b], d->ximat[b], m->body_inertia + 3 * b);
+    spi_body(&I, body_mass_of(m, d, b), d->xipos[b], d->ximat[b], m->body_inertia + 3 * b);
     double Ia[6], Iv[6], c[6];
     spi_mul(Ia, &I, a);
     spi_mul(Iv, &I, v);
