@@ -134,6 +134,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="door-v0:4096", help="env_id:envs_per_gpu (default = BASELINE.json configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pixels", action="store_true", help="also produce the 64x64x3 u8 pixel observation every step (BASELINE.json configs[4])")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--also", default="hammer-v0:8192", help="comma list of extra workloads reported under 'also' (N=1 only; '' = none)")
     args = ap.parse_args()
@@ -177,9 +178,13 @@ def main():
         stream = torch.cuda.current_stream(dev)
         h = env._h
 
+        rgb = torch.empty((n_envs, 64, 64, 3), dtype=torch.uint8, device=dev) if args.pixels else None
+
         def raw_step(i):
             env.abi.check(env.abi.step(h, acts[i % nact].data_ptr(), obs.data_ptr(), rew.data_ptr(), done.data_ptr(), goal.data_ptr(),
                                        stream.cuda_stream))
+            if rgb is not None:
+                env.abi.check(env.abi.render(h, rgb.data_ptr(), stream.cuda_stream))
         env.reset()
         for i in range(warmup):
             raw_step(i)
@@ -232,7 +237,12 @@ def main():
             d_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
             g_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
 
+            rgb_h = torch.empty((n_envs, 64, 64, 3), dtype=torch.uint8).pin_memory() if args.pixels else None
+
             def host_step(i):
+                if rgb is not None:   # pixels of the state this action is chosen from, then the step (both synchronise)
+                    env.abi.check(env.abi.render(h, rgb.data_ptr(), stream.cuda_stream))
+                    rgb_h.copy_(rgb, non_blocking=True)
                 env.abi.check(env.abi.step_host(h, a_h[i & 1].data_ptr(), o_h.data_ptr(), r_h.data_ptr(), d_h.data_ptr(), g_h.data_ptr(),
                                                 stream.cuda_stream))
             for i in range(max(3, warmup // 4)):
@@ -252,7 +262,7 @@ def main():
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 e2e_ms = float(t.item())
             res["e2e"] = {"value": world * n_envs * steps / (e2e_ms * 1e-3), "unit": UNIT,
-                          "h2d_bytes_per_step": n_envs * env.nu * 4, "d2h_bytes_per_step": n_envs * (env.obs_dim * 4 + 4 + 1 + 1)}
+                          "h2d_bytes_per_step": n_envs * env.nu * 4, "d2h_bytes_per_step": n_envs * (env.obs_dim * 4 + 4 + 1 + 1 + (64 * 64 * 3 if args.pixels else 0))}
         env.close()
         return res
 
@@ -266,15 +276,17 @@ def main():
     names = ["smooth_kernel", "collide_kernel", "solve_kernel", "finish_kernel"]
     dom = int(np.argmax(r["phase_ms_per_launch"]))
     bytes_per_launch = ALGO_BYTES[env_id] * n_envs / r["frame_skip"]
+    pix = 64 * 64 * 3 if args.pixels else 0   # algorithmic bytes of the pixel observation, per env-step
     achieved = bytes_per_launch / (r["phase_ms_per_launch"][dom] * 1e-3) / 1e9
-    step_achieved = ALGO_BYTES[env_id] * n_envs / (r["kernel_ms"] * 1e-3) / 1e9
+    step_achieved = (ALGO_BYTES[env_id] + pix) * n_envs / (r["kernel_ms"] * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"{env_id} x{n_envs} envs per GPU, state obs, U(-1,1) actions, auto-reset at the horizon "
                                "(BASELINE.json configs[1])" if args.workload == "door-v0:4096" else
-                               f"{env_id} x{n_envs} envs per GPU, state obs, U(-1,1) actions, auto-reset at the horizon",
+                               f"{env_id} x{n_envs} envs per GPU, state obs{' + 64x64x3 u8 pixel obs (ray-cast)' if args.pixels else ''}, "
+                               "U(-1,1) actions, auto-reset at the horizon",
                    "envs_per_gpu": n_envs, "l2": "flushed between timed steps (256 MiB fill)" if not args.no_flush else "not flushed",
                    "timing": "sum of per-step CUDA-event intervals on the launching stream, max over ranks"},
         "e2e": r["e2e"], "gpu_launches": r["launches"], "clocks": r["clocks"],

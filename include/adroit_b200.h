@@ -96,6 +96,12 @@ int adroit_get_solver(adroit_sim* sim, double* qacc_host, int32_t* ncon_host, in
  * counts the episodes in flight.  Synchronises; the caller all-reduces the 4 numbers across ranks. */
 int adroit_reduce_episode(adroit_sim* sim, int flush_running, double* out4_host, void* stream);
 
+/* env.render() (hammer_v0.py:177-181 -> HeadlessObserver.render, headless_observer.py:34-52, + PlaNet's 128->64 resize):
+ * 64x64 RGB of every env from the reference's free camera, ray-cast against the scene's analytic primitives (no GL on
+ * this box; see csrc/render.cuh for what is and is not reproduced).  rgb_dev: u8 [n, 64, 64, 3].  Draws the frames of the
+ * last forward (as sim.render does).  Enqueued on `stream`, no synchronisation. */
+int adroit_render(adroit_sim* sim, uint8_t* rgb_dev, void* stream);
+
 /* Number of kernel launches this handle has enqueued so far (bench.py's gpu_launches). */
 int64_t adroit_launch_count(const adroit_sim* sim);
 

@@ -24,6 +24,7 @@ SYMBOLS = {
     "reduce_episode": (C.c_int, [_VP, C.c_int, _VP, _VP]),
     "launch_count": (C.c_int64, [_VP]),
     "overflow": (C.c_int, [_VP, _VP, _VP]),
+    "render": (C.c_int, [_VP, _VP, _VP]),
     "profile": (C.c_int, [_VP, C.c_int]),
     "phase_times": (C.c_int, [_VP, _VP, _VP, _VP]),
 }

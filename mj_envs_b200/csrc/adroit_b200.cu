@@ -14,7 +14,7 @@
 #include <vector>
 
 #include "../../include/adroit_b200.h"
-#include "task.cuh"
+#include "render.cuh"
 
 namespace adroit {
 
@@ -506,6 +506,19 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
     PI(m.ld_start, ld_start); PI(m.ld_pair, ld_pair); PI(m.wl_pair, wl_pair); PI(m.tri_ab, tri_ab);
     fix.push_back({A.put(lca), (const void**)&m.lca});
   }
+  {  // pixel path tables (render.cuh)
+    auto ri = B.ints("render_int");
+    m.nrender = (int)ri.size() / 4;
+    if (m.nrender > MAXRG) throw std::string("scene has more render primitives than render.cuh's MAXRG");
+    PI(m.render_int, ri);
+    PR(m.render_real, B.reals("render_real"));
+    auto rc = B.reals("render_cam");
+    for (int i = 0; i < 8; i++) m.render_cam[i] = (T)rc[i];
+    auto lp = B.reals("light_pos"), ld = B.reals("light_diffuse");
+    auto lb = B.ints("light_body");
+    m.light_body = lb.empty() ? 0 : lb[0];
+    for (int i = 0; i < 3; i++) { m.light_pos[i] = lp.size() >= 3 ? (T)lp[i] : T(0); m.light_diffuse[i] = ld.size() >= 3 ? (T)ld[i] : T(0); }
+  }
   PI(m.act_dof, act_dof); PR(m.act_ctrlrange, B.reals("act_ctrlrange")); PR(m.act_gain, B.reals("act_gain")); PR(m.act_bias, B.reals("act_bias"));
   // stash offsets; pointers are patched once the arena is on the device
   for (auto& f : fix) *f.slot = (const void*)f.off;
@@ -868,6 +881,16 @@ int adroit_reduce_episode(adroit_sim* s, int flush_running, double* out4_host, v
   s->launches++;
   CK(cudaMemcpyAsync(out4_host, s->d_out4, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int adroit_render(adroit_sim* s, uint8_t* rgb_dev, void* stream) {
+  if (!rgb_dev) FAIL("rgb is NULL");
+  CK(cudaSetDevice(s->device));
+  if (s->f64) render_kernel<double><<<s->n, RENDER_THREADS, 0, (cudaStream_t)stream>>>(s->md, s->sd, rgb_dev);
+  else render_kernel<float><<<s->n, RENDER_THREADS, 0, (cudaStream_t)stream>>>(s->mf, s->sf, rgb_dev);
+  CK(cudaGetLastError());
+  s->launches++;
   return 0;
 }
 

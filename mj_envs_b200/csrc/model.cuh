@@ -114,12 +114,16 @@ template <typename T> struct DModel {
   const int *ld_start, *ld_pair, *wl_pair, *tri_ab;   // [nv+1], [..] i|j<<8, [..] k|j<<8, [ntri_real] a|b<<8
   const unsigned char* lca;                          // [nv*nv] deepest common ancestor-or-self dof, 255 = none
   const T *act_ctrlrange, *act_gain, *act_bias;
+  const int* render_int;                             // [nrender][4] type, body, par offset of the local pos (-1), is_site
+  const T* render_real;                              // [nrender][19] local pos, local mat, size, rgba (render.cuh)
   int task_int[16];
   T par0[NPARP];
   T touch_size[3];
   T timestep, gravity[3], tolerance, noslip_tolerance, impratio, solref[2], solimp[5], mpr_tolerance, meaninertia;
   T pen_len, tar_len;
   int any_damping;
+  int nrender, light_body;
+  T render_cam[8], light_pos[3], light_diffuse[3];   // mjcf.py::_set_render_camera
 };
 
 // persistent per-env state handed to the kernels.  qpos / qvel / qacc_warmstart / ctrl / per-env model parameters /

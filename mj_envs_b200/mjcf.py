@@ -123,6 +123,7 @@ class Model:
         A = {k: v.copy() for k, v in self.A.items()}
         head, neck, obj = self.name2id("geom", "head"), self.name2id("geom", "neck"), self.name2id("body", "Object")
         A["task_int"][8:12] = [codes[variation_type], obj, head, neck]
+        A["task_int"][12:14] = [A["render_geom_index"][head], A["render_geom_index"][neck]]   # their rows of the render table
         par0 = np.zeros(5)
         par0[:3] = A["par0"][:3]
         if variation_type == "mass":
@@ -736,6 +737,7 @@ def _compile(task, opt, bodies, joints, geoms_all, sites, cams, lights, pairs_x,
 
     m = Model(task=task, names=names, A=A)
     _set_const(m)
+    _set_render_camera(m)
     return m
 
 
@@ -802,6 +804,31 @@ def mass_matrix_numpy(m: Model, qpos, par=None):
         J = jac_numpy(m, xanchor, xaxis, b, c)
         M += A["body_mass"][b] * J[:3].T @ J[:3] + J[3:].T @ Iw @ J[3:]
     return M
+
+
+def _set_render_camera(m: Model):
+    """Free-camera constants of the reference's headless pixel path (headless_observer.py:20-31,59-67; pen_v0.py:163-177),
+    evaluated once at qpos0 like the reference does at construction:
+      lookat    = per-axis median of the geom world positions  [EXT mujoco-py MjRenderContext._init_camera]; the mesh geoms
+                  are absent here, so the median runs over the primitive geoms of the render table
+      azimuth   = 90, distance = 4.5                             (headless_observer.py:29-30)
+      elevation = -45 + deg(acos(v_x / v_z)) / 2, v = xpos[obj body] - cam_xpos[last camera]   (:61-65)
+      fovy      = 45 (MuJoCo default), frame 640x480, centre crop 128x128 (:38,44)
+    np.arccos outside [-1, 1] gives NaN in the reference (MuJoCo then renders with a garbage camera); this build clamps
+    the argument and records that it did so in render_cam[7].
+    render_cam = [lookat x, y, z, azimuth, elevation, distance, fovy, clamped]."""
+    A = m.A
+    xpos, xquat, _, _ = fk_numpy(m, np.zeros(m.nv))
+    ri, rr = A["render_int"], A["render_real"]
+    gp = np.array([xpos[b] + quat_to_mat(xquat[b]) @ r[:3] for (_, b, _, site), r in zip(ri, rr) if not site])
+    lookat = np.median(gp, axis=0)
+    cb = int(A["cam_body"][-1])
+    cam = xpos[cb] + quat_to_mat(xquat[cb]) @ A["cam_pos"][-1]
+    v = xpos[int(A["render_obj_body"][0])] - cam
+    ratio = v[0] / v[2] if v[2] != 0 else 0.0
+    clamped = float(abs(ratio) > 1)
+    elev = -45.0 + np.rad2deg(np.arccos(np.clip(ratio, -1.0, 1.0))) / 2
+    A["render_cam"] = np.array([lookat[0], lookat[1], lookat[2], 90.0, elev, 4.5, 45.0, clamped])
 
 
 def _set_const(m: Model):

@@ -135,6 +135,14 @@ class AdroitVecEnv:
         self.abi.check(self.abi.step_host(self._h, action.ctypes.data, obs.ctypes.data, reward.ctypes.data, done.ctypes.data,
                                           goal.ctypes.data, self._stream()))
 
+    def render(self, out: torch.Tensor | None = None):
+        """64x64 RGB pixel observation of every env, u8 [N, 64, 64, 3] (hammer_v0.py:177-181 -> HeadlessObserver.render,
+        headless_observer.py:34-52, then PlaNet's 128->64 resize); ray-cast on the device, see csrc/render.cuh."""
+        if out is None:
+            out = torch.empty((self.num_envs, 64, 64, 3), dtype=torch.uint8, device=self.device)
+        self.abi.check(self.abi.render(self._h, out.data_ptr(), self._stream()))
+        return out
+
     def get_obs(self):
         self.abi.check(self.abi.get_obs(self._h, self._obs.data_ptr(), self._stream()))
         return self._obs.clone()
