@@ -19,6 +19,9 @@
 namespace adroit {
 
 enum { MODE_STEP = 0, MODE_RESET = 1, MODE_FORWARD = 2 };
+#ifndef ADROIT_DEFAULT_SUBBATCHES
+#define ADROIT_DEFAULT_SUBBATCHES 4
+#endif
 
 struct PArgs {
   const float* action;        // smooth: action map (hammer_v0.py:55-59) when non-null
@@ -33,6 +36,7 @@ struct PArgs {
   int epilogue;               // finish: reward / success / episode counters / auto-reset decision (last substep of a step)
   int write_obs;              // finish: pack the observation
   int debug;                  // export introspection copies (G_DBG_*)
+  int env0, env1;             // this launch covers envs [env0, env1): one sub-batch of the handle (run_t)
 };
 
 #define VR(V, F) Reg{(V) * NVP, NVP, (F)}
@@ -101,8 +105,8 @@ template <typename T> __device__ void episode_finish(const DModel<T>& m, const D
 #define PHASE_PROLOGUE(MAP)                                                                                             \
   extern __shared__ __align__(16) unsigned char smem_raw[];                                                              \
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;                                                            \
-  const int env = blockIdx.x * WPB + warp;                                                                               \
-  if (env >= st.n) return;                        /* no block-wide barrier anywhere in a phase kernel */                 \
+  const int env = a.env0 + blockIdx.x * WPB + warp;                                                                      \
+  if (env >= a.env1) return;                      /* no block-wide barrier anywhere in a phase kernel */                 \
   if (a.mask && !a.mask[env]) return;                                                                                    \
   T* sm_ = reinterpret_cast<T*>(smem_raw) + (size_t)warp * map_st<MAP>();                                                \
   int* smi_ = reinterpret_cast<int*>(smem_raw + (size_t)WPB * map_st<MAP>() * sizeof(T)) + warp * map_si<MAP>();         \
@@ -406,6 +410,12 @@ struct adroit_sim {
   int64_t launches = 0;
   bool profile = false;
   std::vector<cudaEvent_t> prof_ev[4];   // event pairs per phase, pending accumulation
+  // sub-batch pipelining (run_t): the envs are split into nsub contiguous ranges, each advanced by its own chain of
+  // phase kernels on its own stream, so that the tail of one range's kernel overlaps the other ranges' kernels
+  int nsub = 1;
+  std::vector<cudaStream_t> sub_stream;
+  std::vector<cudaEvent_t> sub_done;
+  cudaEvent_t fork_ev = nullptr;
 };
 
 namespace {
@@ -581,7 +591,8 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
 template <typename T, class MAP, typename K>
 int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {
   size_t smem = WPB * map_bytes<T, MAP>();
-  int blocks = (st.n + WPB - 1) / WPB;
+  int blocks = (a.env1 - a.env0 + WPB - 1) / WPB;
+  if (blocks <= 0) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (s->profile) {
     CK(cudaEventCreate(&e0));
@@ -616,12 +627,10 @@ template <typename T> int forward_pass(adroit_sim* s, const DModel<T>& m, const 
   return 0;
 }
 
+// the launches of one request over the env range [a.env0, a.env1) on one stream
 template <typename T>
-int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, const float* action, const uint8_t* mask, float* obs, float* reward,
-          uint8_t* done, uint8_t* goal, int debug, cudaStream_t stream) {
-  PArgs a;
-  memset(&a, 0, sizeof a);
-  a.debug = debug;
+int run_range(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, PArgs a, const float* action, const uint8_t* mask, float* obs,
+              float* reward, uint8_t* done, uint8_t* goal, cudaStream_t stream) {
   if (mode == MODE_FORWARD) {            // sim.forward()
     a.mask = mask;
     return forward_pass(s, m, st, a, stream);
@@ -643,6 +652,38 @@ int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, cons
     PArgs r = a;
     r.mask = st.reset_flag; r.reset = 1; r.obs = obs; r.write_obs = obs != nullptr;
     if (forward_pass(s, m, st, r, stream)) return 1;
+  }
+  return 0;
+}
+
+// Envs are independent, so a request is issued as nsub contiguous sub-batches, each a chain of phase kernels on its own
+// stream (forked from / joined to the caller's stream with events: no host sync).  A phase kernel of one sub-batch
+// then fills the SMs that the last, partly empty wave of another sub-batch's kernel leaves idle, and kernels bound by
+// different resources (registers: collide, shared memory: solve) share an SM.  Per-phase profiling and debug exports
+// use one range on the caller's stream.
+template <typename T>
+int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, const float* action, const uint8_t* mask, float* obs, float* reward,
+          uint8_t* done, uint8_t* goal, int debug, cudaStream_t stream) {
+  PArgs a;
+  memset(&a, 0, sizeof a);
+  a.debug = debug;
+  int nsub = (s->profile || debug) ? 1 : s->nsub;
+  int per = ((st.n + nsub - 1) / nsub + WPB - 1) / WPB * WPB;
+  if (per < 64 * WPB) { per = 64 * WPB; }          // never less than 64 blocks per launch
+  nsub = (st.n + per - 1) / per;
+  if (nsub <= 1) {
+    a.env0 = 0; a.env1 = st.n;
+    return run_range(s, m, st, mode, a, action, mask, obs, reward, done, goal, stream);
+  }
+  CK(cudaEventRecord(s->fork_ev, stream));
+  for (int c = 0; c < nsub; c++) {
+    cudaStream_t ss = s->sub_stream[c];
+    CK(cudaStreamWaitEvent(ss, s->fork_ev, 0));
+    a.env0 = c * per;
+    a.env1 = (c + 1) * per < st.n ? (c + 1) * per : st.n;
+    if (run_range(s, m, st, mode, a, action, mask, obs, reward, done, goal, ss)) return 1;
+    CK(cudaEventRecord(s->sub_done[c], ss));
+    CK(cudaStreamWaitEvent(stream, s->sub_done[c], 0));
   }
   return 0;
 }
@@ -717,6 +758,21 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
   s->allocs.push_back(s->arena.dev);
   CK(cudaMemcpy(s->arena.dev, s->arena.host.data(), s->arena.host.size(), cudaMemcpyHostToDevice));
   if (s->f64 ? configure_kernels<double>() : configure_kernels<float>()) { delete s; return 1; }
+  {
+    const char* e = getenv("ADROIT_SUBBATCHES");
+    // default: sub-batches of >= 2048 envs, at most ADROIT_DEFAULT_SUBBATCHES of them (measured: profiles/r3_subbatches.txt)
+    int want = e ? atoi(e) : (n_envs / 2048 < ADROIT_DEFAULT_SUBBATCHES ? n_envs / 2048 : ADROIT_DEFAULT_SUBBATCHES);
+    s->nsub = want < 1 ? 1 : (want > 16 ? 16 : want);
+    CK(cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
+    for (int c = 0; c < s->nsub; c++) {
+      cudaStream_t ss;
+      cudaEvent_t ev;
+      CK(cudaStreamCreateWithFlags(&ss, cudaStreamNonBlocking));
+      CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+      s->sub_stream.push_back(ss);
+      s->sub_done.push_back(ev);
+    }
+  }
   int rc;
   if (s->f64) {
     patch_model(s->md, s->arena.dev);
@@ -749,6 +805,9 @@ void adroit_destroy(adroit_sim* s) {
   if (!s) return;
   cudaSetDevice(s->device);
   for (auto& v : s->prof_ev) for (cudaEvent_t e : v) cudaEventDestroy(e);
+  for (cudaStream_t ss : s->sub_stream) cudaStreamDestroy(ss);
+  for (cudaEvent_t e : s->sub_done) cudaEventDestroy(e);
+  if (s->fork_ev) cudaEventDestroy(s->fork_ev);
   for (void* p : s->allocs) cudaFree(p);
   if (s->stage) cudaFree(s->stage);
   if (s->d_action) cudaFree(s->d_action);
