@@ -69,13 +69,13 @@ struct MapSolve {
 };
 // M^-1 is staged (read-only) for the noslip sweeps; the same shared-memory region then holds the (M + hB) factor
 struct MapFinish {
-  static constexpr int NT = 20, NI = 2;
+  static constexpr int NT = 20, NI = 3;
   static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),
                                  VR(V_QACC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_QFC, R_IN | R_OUT), VR(V_T1, R_ZERO),
                                  VR(V_DINV, R_ZERO), Reg{SM_T + G_MINV, NTRI, R_IN}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},
                                  Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}, Reg{O_AV, CROWS, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
                                  Reg{O_CBT, MAXCON * 3, R_IN}, Reg{O_EF, MAXCON * 6, R_IN | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
-  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON, R_IN}};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON, R_IN}, Reg{I_SURV, MAXSURV, 0}};
 };
 #undef VR
 

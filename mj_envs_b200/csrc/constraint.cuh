@@ -669,79 +669,139 @@ template <class CX> PHASE_FN void newton(CX& c) {
 }
 
 // ---------------------------------------------------------------- noslip (Gauss-Seidel on friction rows, matrix-free)
+// The sweep is MuJoCo's row-by-row Gauss-Seidel, evaluated without walking the rows one at a time:
+//   * u = M^-1 J^T f lives in two registers per lane (dof lane, lane + 32) for the whole pass;
+//   * friction-loss rows: every lane evaluates the update of ITS row against the current u; the first row (in row
+//     order) whose force would change is applied (one column of M^-1 per lane) and the evaluation repeats behind it.
+//     Rows in front of the first change are untouched by definition, so this is exactly the serial sweep, at one
+//     round per CHANGED row instead of one per row (saturated friction rows -- moving joints -- never change);
+//   * contact tangents: a compact list of tangent rows; the Jacobian row and its M^-1 image are prefetched one
+//     tangent ahead, so the global loads are off the dependent chain  dot -> warp sum -> clamp -> update.
 template <class CX> PHASE_FN void noslip(CX& c) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
   const int nv = m.nv, lane = c.lane;
+  const unsigned FULL = 0xffffffffu;
   const T *Minv = c.template G<G_MINV>(), *JR = c.template G<G_JR>(), *qas = c.template V<V_QAS>();
   T *u = c.template V<V_GRAD>(), *tmp = c.template V<V_SEARCH>(), *qfc = c.template V<V_QFC>(), *YT = c.template G<G_YT>();
   const int* sinfo = c.template I<I_SINFO>();
   const T *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>(), *cmu = c.template S<O_CMU>(), *cbt = c.template S<O_CBT>();
   T *sforce = c.template S<O_SFORCE>(), *ef = c.template S<O_EF>();
+  int* trow = c.template I<I_SURV>();          // compact tangent list: contact-frame row 4*ci + 1 + k
   // u = M^-1 J^T f  (qfc holds J^T f from the last constraint_update)
   symv(Minv, qfc, u, nv, lane);
-  // Yt[ci][k] = M^-1 Jt_k^T and K1 = 4 mu_k^2 Jt_k.Yt_k (kept in O_AV[ci*4+1+k])
+  // Y[t] = M^-1 Jt^T and K1[t] = 4 mu^2 Jt.Y[t] for every tangent row t
   T* K1 = c.template S<O_AV>();
+  int ntan = 0;
   for (int ci = 0; ci < c.ncon; ci++) {
     int dim = c.template I<I_CDIM>()[ci];
     for (int k = 0; k + 2 <= dim && k < 3; k++) {
       const T* Jt = JR + (4 * ci + 1 + k) * NVP;
       _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
       __syncwarp();
-      T* Y = YT + (3 * ci + k) * NVP;
+      T* Y = YT + ntan * NVP;
       symv(Minv, tmp, Y, nv, lane);
       __syncwarp();
       T dsum = 0;
       _Pragma("unroll 1") for (int i = lane; i < nv; i += 32) dsum += Y[i] * tmp[i];
       dsum = warp_sum(dsum);
-      if (lane == 0) K1[4 * ci + 1 + k] = 4 * cmu[3 * ci + k] * cmu[3 * ci + k] * dsum;
+      if (lane == 0) { K1[ntan] = 4 * cmu[3 * ci + k] * cmu[3 * ci + k] * dsum; trow[ntan] = 4 * ci + 1 + k; }
+      ntan++;
       __syncwarp();
     }
   }
   __syncwarp();
+  // registers: u, qacc_smooth by dof; the lane's friction rows (row lane -> set 0, row lane + 32 -> set 1)
+  T u0, u1, q0, q1;
+  load_vec(u, nv, lane, u0, u1);
+  load_vec(qas, nv, lane, q0, q1);
+  bool val[2];
+  int dj[2];
+  T qd[2], sa[2], Aii[2], fl[2], f[2];
+#pragma unroll
+  for (int s = 0; s < 2; s++) {
+    int r = lane + 32 * s;
+    int info = r < c.nsimple ? sinfo[r] : -1;
+    val[s] = r < c.nsimple && (info & 3) == S_FRICTION;
+    dj[s] = val[s] ? (info >> 2) & 1023 : 0;
+    qd[s] = qas[dj[s]];
+    sa[s] = val[s] ? saref[r] : T(0);
+    Aii[s] = Minv[tri(dj[s], dj[s])];
+    fl[s] = val[s] ? sfl[r] : T(0);
+    f[s] = val[s] ? sforce[r] : T(0);
+  }
+  const bool ident = __all_sync(FULL, (!val[0] || dj[0] == lane) && (!val[1] || dj[1] == lane + 32));   // row r <-> dof r
+  const bool any1 = __any_sync(FULL, val[1]);
   const T scale = T(1) / (m.meaninertia * (nv > 1 ? nv : 1));
   int sweeps = 0;
   for (int iter = 0; iter < m.noslip_iterations; iter++) {
     T improvement = 0;
-    for (int r = 0; r < c.nsimple; r++) {
-      int info = sinfo[r];
-      if ((info & 3) != S_FRICTION) break;  // friction rows come first
-      int dj = (info >> 2) & 1023;
-      T res = u[dj] + qas[dj] - saref[r], Aii = Minv[tri(dj, dj)], old = sforce[r], fl = sfl[r];
-      T f = tclamp(old - res / Aii, -fl, fl), delta = f - old;
-      __syncwarp();
-      if (delta != 0) {
-        _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) u[j] += delta * sym_get(Minv, j, dj);
-        if (lane == 0) sforce[r] = f;
-        improvement -= T(0.5) * delta * delta * Aii + delta * res;
-      }
-      __syncwarp();
+    int start = 0;
+    while (true) {
+      T res[2] = {0, 0}, fn[2] = {0, 0}, de[2] = {0, 0};
+      bool nz[2] = {false, false};
+      auto eval = [&](int s) {
+        T ud;
+        if (ident) ud = s ? u1 : u0;
+        else {
+          T a = __shfl_sync(FULL, u0, dj[s] & 31), b = __shfl_sync(FULL, u1, dj[s] & 31);
+          ud = dj[s] < 32 ? a : b;
+        }
+        res[s] = ud + qd[s] - sa[s];
+        fn[s] = tclamp(f[s] - res[s] / Aii[s], -fl[s], fl[s]);
+        de[s] = fn[s] - f[s];
+        nz[s] = val[s] && lane + 32 * s >= start && de[s] != 0;
+      };
+      eval(0);
+      if (any1) eval(1);
+      unsigned b0 = __ballot_sync(FULL, nz[0]), b1 = any1 ? __ballot_sync(FULL, nz[1]) : 0u;
+      if (!(b0 | b1)) break;
+      const int set = b0 ? 0 : 1, src = __ffs(b0 ? b0 : b1) - 1;
+      const T d = __shfl_sync(FULL, set ? de[1] : de[0], src), rs = __shfl_sync(FULL, set ? res[1] : res[0], src);
+      const T A = __shfl_sync(FULL, set ? Aii[1] : Aii[0], src);
+      const int col = __shfl_sync(FULL, set ? dj[1] : dj[0], src);
+      if (lane < nv) u0 += d * sym_get(Minv, lane, col);
+      if (lane + 32 < nv) u1 += d * sym_get(Minv, lane + 32, col);
+      if (lane == src) { if (set) f[1] = fn[1]; else f[0] = fn[0]; }
+      improvement -= T(0.5) * d * d * A + d * rs;
+      start = src + 32 * set + 1;
     }
-    for (int ci = 0; ci < c.ncon; ci++) {
-      int dim = c.template I<I_CDIM>()[ci];
-      for (int k = 0; k + 2 <= dim && k < 3; k++) {
-        const T* Jt = JR + (4 * ci + 1 + k) * NVP;
-        T s = 0;
-        _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) s += Jt[j] * (u[j] + qas[j]);
+    if (ntan > 0) {
+      const T *Jn = JR + trow[0] * NVP;
+      T jn0, jn1, yn0, yn1;
+      load_vec(Jn, nv, lane, jn0, jn1);
+      load_vec(YT, nv, lane, yn0, yn1);
+      _Pragma("unroll 1") for (int t = 0; t < ntan; t++) {
+        const T j0 = jn0, j1 = jn1, y0 = yn0, y1 = yn1;
+        const int row = trow[t], ci = row >> 2, k = (row & 3) - 1;
+        if (t + 1 < ntan) {
+          load_vec(JR + trow[t + 1] * NVP, nv, lane, jn0, jn1);
+          load_vec(YT + (t + 1) * NVP, nv, lane, yn0, yn1);
+        }
+        T s = j0 * (u0 + q0);
+        if (nv > 32) s += j1 * (u1 + q1);
         s = warp_sum(s);
-        T mu = cmu[3 * ci + k], g = 2 * mu * s - 2 * cbt[3 * ci + k], k1 = K1[4 * ci + 1 + k];
+        T mu = cmu[3 * ci + k], g = 2 * mu * s - 2 * cbt[3 * ci + k], k1 = K1[t];
         T f0 = ef[6 * ci + 2 * k], f1 = ef[6 * ci + 2 * k + 1], mid = T(0.5) * (f0 + f1), yold = T(0.5) * (f0 - f1), y = yold;
         if (k1 >= T(1e-15)) y = tclamp(yold - g / k1, -mid, mid);
         else y = 0;
         T dy = y - yold;
         __syncwarp();
         if (dy != 0) {
-          const T* Y = YT + (3 * ci + k) * NVP;
-          _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) u[j] += 2 * mu * dy * Y[j];
+          u0 += 2 * mu * dy * y0;
+          u1 += 2 * mu * dy * y1;
           if (lane == 0) { ef[6 * ci + 2 * k] = mid + y; ef[6 * ci + 2 * k + 1] = mid - y; }
           improvement -= T(0.5) * k1 * dy * dy + g * dy;
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
     sweeps = iter + 1;
     if (scale * improvement < m.noslip_tolerance) break;
   }
+#pragma unroll
+  for (int s = 0; s < 2; s++)
+    if (val[s]) sforce[lane + 32 * s] = f[s];
   if (lane == 0) c.gi[GI_NSLIP] = sweeps;
   __syncwarp();
 }
