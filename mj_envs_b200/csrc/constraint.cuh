@@ -339,24 +339,26 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   T *sforce = c.template S<O_SFORCE>(), *qfc = c.template V<V_QFC>();
   T cost = 0;
   bool changed = false;   // did any row / pyramid edge move between the quadratic and the inactive (or linear) zone?
+  bool flipped = false;   // did a friction row jump from one linear zone to the other (through the quadratic one)?
   if (want_qfc) {
     _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;
     __syncwarp();
   }
   _Pragma("unroll 1") for (int r = c.lane; r < c.nsimple; r += 32) {
-    int info = sinfo[r] & 0x1fff, old_state = (sinfo[r] >> 13) & 1;
+    int info = sinfo[r] & 0x1fff, old_state = (sinfo[r] >> 13) & 1, old_side = (sinfo[r] >> 14) & 1;
     T jar = simple_dot(m, info, qacc) - saref[r], D = sD[r], f;
-    int state;
+    int state, side = 0;   // side: which of the two linear zones of a friction row (no effect on the Hessian)
     if ((info & 3) == S_FRICTION) {
       T fl = sfl[r], rf = fl / D;
       if (jar <= -rf) { f = fl; state = 0; cost += -T(0.5) * rf * fl - fl * jar; }
-      else if (jar >= rf) { f = -fl; state = 0; cost += -T(0.5) * rf * fl + fl * jar; }
+      else if (jar >= rf) { f = -fl; state = 0; side = 1; cost += -T(0.5) * rf * fl + fl * jar; }
       else { f = -D * jar; state = 1; cost += T(0.5) * D * jar * jar; }
     } else if (jar < 0) { f = -D * jar; state = 1; cost += T(0.5) * D * jar * jar; }
     else { f = 0; state = 0; }
     sforce[r] = f;
-    sinfo[r] = info | (state << 13);
+    sinfo[r] = info | (state << 13) | (side << 14);
     changed |= state != old_state;
+    flipped |= side != old_side;
     if (want_qfc && f != 0) {
       int kind = info & 3, id = (info >> 2) & 1023, up = (info >> 12) & 1;
       if (kind == S_FRICTION) atomicAdd(qfc + id, f);
@@ -397,6 +399,7 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
     cmask[ci] = emask;
   }
   c.nchanged = __any_sync(0xffffffffu, changed);
+  c.nflipped = __any_sync(0xffffffffu, flipped);
   __syncwarp();
   if (want_qfc && c.ncon > 0) {
     // frame forces F[ci][4] into O_AV (scratch use), then qfc[j] += sum_r Jr[r][j] F[r]
@@ -560,6 +563,9 @@ template <class CX> PHASE_FN void build_hessian(CX& c) {
   }
 }
 
+#ifndef ADROIT_STOP_ON_QUADRATIC
+#define ADROIT_STOP_ON_QUADRATIC 1
+#endif
 #ifndef ADROIT_LOCKSTEP
 #define ADROIT_LOCKSTEP 0
 #endif
@@ -579,20 +585,23 @@ template <class CX> PHASE_FN void newton(CX& c) {
     _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) s += T(0.5) * (Maa[j] - qfs[j]) * (a[j] - qas[j]);
     return warp_sum(s);
   };
-  symv(M, warm, Ma, nv, lane);
-  contact_frame_mul(c, warm, ac);
-  __syncwarp();
-  T cost_ws = constraint_update(c, warm, false) + gauss(warm, Ma);
+  // (qacc_smooth first, so that the states / forces / J^T f left behind are those of the warm start, the usual winner)
   contact_frame_mul(c, qas, ac);
   __syncwarp();
   T cost_sm = constraint_update(c, qas, false);
-  bool use_ws = cost_ws < cost_sm;
+  symv(M, warm, Ma, nv, lane);
+  contact_frame_mul(c, warm, ac);
+  __syncwarp();
+  T cost = constraint_update(c, warm, true) + gauss(warm, Ma);
+  bool use_ws = cost < cost_sm;
   _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) qacc[j] = use_ws ? warm[j] : qas[j];
   __syncwarp();
-  symv(M, qacc, Ma, nv, lane);
-  contact_frame_mul(c, qacc, ac);
-  __syncwarp();
-  T cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
+  if (!use_ws) {
+    symv(M, qacc, Ma, nv, lane);
+    contact_frame_mul(c, qacc, ac);
+    __syncwarp();
+    cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
+  }
   int iters = 0;
   bool refactor = true;
   bool done = false;
@@ -662,6 +671,11 @@ template <class CX> PHASE_FN void newton(CX& c) {
     // quadratic convergence makes the step after such an iteration a no-op, so stop there instead of burning a factorisation
     T floor_ = sizeof(T) == 4 ? T(2e-6) * tabs(cost) : T(0);
     if (scale * (old - cost) < m.tolerance || (old - cost) < floor_) break;
+#if ADROIT_STOP_ON_QUADRATIC
+    // no row / edge changed state along the step: the cost was exactly quadratic on it and the Newton step landed on
+    // its minimiser, so the next iteration could only polish rounding error
+    if (!refactor && !c.nflipped) break;
+#endif
     done = false;
     } while (0);
   }

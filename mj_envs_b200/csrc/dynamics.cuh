@@ -55,9 +55,9 @@ template <typename T_, class MAP_> struct Ctx {
   int* gib;  // this env's context block (int): [SM_I | GI_TOTAL]
   int* gi;   // = gib + SM_I
   int lane;
-  int ncon, nsimple, nchanged;
+  int ncon, nsimple, nchanged, nflipped;
   __device__ Ctx(const DModel<T>& mm, T* sm_, int* smi_, T* gb_, int* gib_, int lane_)
-      : m(mm), sm(sm_), smi(smi_), gb(gb_), gib(gib_), gi(gib_ + SM_I), lane(lane_), ncon(0), nsimple(0), nchanged(1) {}
+      : m(mm), sm(sm_), smi(smi_), gb(gb_), gib(gib_), gi(gib_ + SM_I), lane(lane_), ncon(0), nsimple(0), nchanged(1), nflipped(0) {}
   template <int O> static constexpr bool in_smem() { return map_soff<MAP>(O) >= 0; }
   template <int O> DI T* S() const {
     constexpr int so = map_soff<MAP>(O);
