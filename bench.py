@@ -216,6 +216,11 @@ def main():
                "kernel_ms": float(ms.mean()), "clocks": clocks, "wall_s": wall, "stats": stats.tolist(), "overflow": overflow.tolist(),
                "nu": env.nu, "obs_dim": env.obs_dim}
         # per-phase device time of the same workload (CUDA events around every phase-kernel launch, on the launching stream)
+        # (every measurement section restarts from reset + the same warm-up, so that all of them time the same steps of
+        # the episodes: the cost of a step depends on where in the episode it is)
+        env.reset()
+        for i in range(warmup):
+            raw_step(i)
         env.profile(True)
         psteps = min(steps, 40)
         for i in range(psteps):
@@ -245,7 +250,8 @@ def main():
                     rgb_h.copy_(rgb, non_blocking=True)
                 env.abi.check(env.abi.step_host(h, a_h[i & 1].data_ptr(), o_h.data_ptr(), r_h.data_ptr(), d_h.data_ptr(), g_h.data_ptr(),
                                                 stream.cuda_stream))
-            for i in range(max(3, warmup // 4)):
+            env.reset()
+            for i in range(max(3, warmup)):
                 host_step(i)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             barrier()
