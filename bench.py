@@ -226,7 +226,7 @@ def main():
         for i in range(psteps):
             if flush is not None:
                 flush.fill_(i & 0xFF)
-            raw_step(warmup + steps + i)
+            raw_step(warmup + i)
         pms, pn = env.phase_times()
         env.profile(False)
         res["phase_ms_per_launch"] = (pms / (psteps * env.frame_skip)).tolist()   # the masked reset pass (a few us) is folded in
@@ -234,9 +234,7 @@ def main():
         res["frame_skip"] = env.frame_skip
         if with_e2e:
             # end to end through the reference-facing call: pinned HOST buffers, H2D action + D2H obs/reward/done/goal every step
-            a_h = [torch.empty((n_envs, env.nu), dtype=torch.float32).pin_memory() for _ in range(2)]
-            for b in a_h:
-                b.copy_(torch.rand((n_envs, env.nu)) * 2 - 1)
+            a_h = [acts[j].cpu().pin_memory() for j in range(nact)]     # the same action sequence as the device-resident run
             o_h = torch.empty((n_envs, env.obs_dim), dtype=torch.float32).pin_memory()
             r_h = torch.empty(n_envs, dtype=torch.float32).pin_memory()
             d_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
@@ -248,7 +246,7 @@ def main():
                 if rgb is not None:   # pixels of the state this action is chosen from, then the step (both synchronise)
                     env.abi.check(env.abi.render(h, rgb.data_ptr(), stream.cuda_stream))
                     rgb_h.copy_(rgb, non_blocking=True)
-                env.abi.check(env.abi.step_host(h, a_h[i & 1].data_ptr(), o_h.data_ptr(), r_h.data_ptr(), d_h.data_ptr(), g_h.data_ptr(),
+                env.abi.check(env.abi.step_host(h, a_h[i % nact].data_ptr(), o_h.data_ptr(), r_h.data_ptr(), d_h.data_ptr(), g_h.data_ptr(),
                                                 stream.cuda_stream))
             env.reset()
             for i in range(max(3, warmup)):
@@ -258,7 +256,7 @@ def main():
             e0.record(stream)
             acc = 0.0
             for i in range(steps):
-                host_step(i)
+                host_step(warmup + i)
                 acc += float(r_h[0])            # the host consumes the step's result
             e1.record(stream)
             barrier()

@@ -248,7 +248,7 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
 
   // contacts: contact-frame Jacobian rows (both layouts), frame velocity, impedance
   const T *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>();
-  T *JR = c.template G<G_JR>(), *JT = c.template G<G_JT>();
+  T *JR = c.template G<G_JR>();
   T *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>(), *ef = c.template S<O_EF>();
   for (int ci = 0; ci < c.ncon; ci++) {
     const T* C = c.template G<G_CON>() + 16 * ci;
@@ -276,12 +276,12 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
           for (int a4 = 0; a4 < 4; a4++) vsum[a4] += row[a4] * qvel[j];
         }
       }
-      for (int a4 = 0; a4 < 4; a4++) {
-        JR[(4 * ci + a4) * NVP + j] = row[a4];
-        JT[j * CROWS + 4 * ci + a4] = row[a4];
-      }
+      for (int a4 = 0; a4 < 4; a4++) JR[(4 * ci + a4) * NVP + j] = row[a4];
     }
-    for (int a4 = 0; a4 < 4; a4++) vsum[a4] = warp_sum(vsum[a4]);
+    {
+      T t = warp_sum4(vsum[0], vsum[1], vsum[2], vsum[3], c.lane);
+      for (int a4 = 0; a4 < 4; a4++) vsum[a4] = __shfl_sync(0xffffffffu, t, 8 * a4);
+    }
     if (c.lane == 0) {
       T dist = C[0], mg = C[13], imp = impedance(m, dist, mg);
       T tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
@@ -310,15 +310,26 @@ template <typename T> DI T simple_dot(const DModel<T>& m, int info, const T* x) 
   }
   return up ? -s : s;
 }
-// contact-frame products  out[ci][a] = Jf[ci][a] . x   (lanes over rows, dof-major layout -> coalesced)
+// contact-frame products  out[ci][a] = Jf[ci][a] . x   (lanes over dofs: coalesced row reads, the four rows of a
+// contact reduced together)
 template <class CX> SUB_FN void contact_frame_mul(CX& c, const typename CX::real* x, typename CX::real* out) {
   using T = typename CX::real;
-  const T* JT = c.template G<G_JT>();
-  int nrows = 4 * c.ncon;
-  _Pragma("unroll 1") for (int r = c.lane; r < nrows; r += 32) {
-    T s = 0;
-    for (int j = 0; j < c.m.nv; j++) s += JT[j * CROWS + r] * x[j];
-    out[r] = s;
+  const T* JR = c.template G<G_JR>();
+  const int nv = c.m.nv, lane = c.lane;
+  T x0, x1;
+  load_vec(x, nv, lane, x0, x1);
+#pragma unroll 2
+  for (int ci = 0; ci < c.ncon; ci++) {
+    const T* J = JR + 4 * ci * NVP;
+    T v[4];
+#pragma unroll
+    for (int a = 0; a < 4; a++) v[a] = J[a * NVP + lane] * x0;          // pad columns of J are zero
+    if (nv > 32 && lane < NVP - 32) {
+#pragma unroll
+      for (int a = 0; a < 4; a++) v[a] += J[a * NVP + 32 + lane] * x1;
+    }
+    T t = warp_sum4(v[0], v[1], v[2], v[3], lane);
+    if ((lane & 7) == 0) out[4 * ci + (lane >> 3)] = t;
   }
 }
 // edge e of contact ci: value of (Jn + sign*mu_k*Jt_k).x given the frame product fx[4]
@@ -327,6 +338,46 @@ template <typename T> DI T edge_val(const T* fx, const T* mu, int dim, int e, T&
   k = e >> 1;
   sign = (e & 1) ? T(-1) : T(1);
   return fx[0] + sign * mu[k] * fx[k + 1];
+}
+
+// frame force F[ci][4] (normal, 2 tangents, torsion) of every contact from its pyramid edge forces
+template <class CX> DI void frame_forces(CX& c, typename CX::real* F) {
+  using T = typename CX::real;
+  const T *ef = c.template S<O_EF>(), *cmu = c.template S<O_CMU>();
+  _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
+    const int dim = c.template I<I_CDIM>()[ci];
+    const T* f = ef + 6 * ci;
+    T e[6];
+#pragma unroll
+    for (int q = 0; q < 6; q++) e[q] = f[q];
+    T out[4] = {e[0], 0, 0, 0};
+    if (dim > 1) {
+      out[0] = e[0] + e[1];
+      out[1] = cmu[3 * ci] * (e[0] - e[1]);
+      if (dim > 2) { out[0] += e[2] + e[3]; out[2] = cmu[3 * ci + 1] * (e[2] - e[3]); }
+      if (dim > 3) { out[0] += e[4] + e[5]; out[3] = cmu[3 * ci + 2] * (e[4] - e[5]); }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; q++) F[4 * ci + q] = out[q];
+  }
+}
+// qfc[j] += sum_r Jf[r][j] F[r]   (lanes over dofs; contacts without force are skipped)
+template <class CX> DI void add_jt_force(CX& c, const typename CX::real* F, typename CX::real* qfc) {
+  using T = typename CX::real;
+  const T* JR = c.template G<G_JR>();
+  const int nv = c.m.nv, lane = c.lane;
+  T a0 = 0, a1 = 0;
+#pragma unroll 2
+  for (int ci = 0; ci < c.ncon; ci++) {
+    Vec4<T> f = ld4(F + 4 * ci);
+    if (f.v[0] == 0 && f.v[1] == 0 && f.v[2] == 0 && f.v[3] == 0) continue;   // warp-uniform (shared-memory values)
+    const T* J = JR + 4 * ci * NVP;
+    a0 += J[lane] * f.v[0] + J[NVP + lane] * f.v[1] + J[2 * NVP + lane] * f.v[2] + J[3 * NVP + lane] * f.v[3];
+    if (nv > 32 && lane < NVP - 32)
+      a1 += J[32 + lane] * f.v[0] + J[NVP + 32 + lane] * f.v[1] + J[2 * NVP + 32 + lane] * f.v[2] + J[3 * NVP + 32 + lane] * f.v[3];
+  }
+  if (lane < nv) qfc[lane] += a0;
+  if (lane + 32 < nv) qfc[lane + 32] += a1;
 }
 
 // cost, forces and states at the point whose frame accelerations are in O_AC and dof accelerations in `qacc`.
@@ -375,26 +426,33 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   T *ef = c.template S<O_EF>(), *W = c.template S<O_W>();
   int* cmask = c.template I<I_CMASK>();
   _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
-    int dim = c.template I<I_CDIM>()[ci], ne = n_edges<T>(dim);
-    T D = cD[ci], w[7] = {0, 0, 0, 0, 0, 0, 0};
+    const int dim = c.template I<I_CDIM>()[ci], ne = n_edges<T>(dim);
+    const T D = cD[ci], an = carefn[ci];
+    const Vec4<T> fx = ld4(ac + 4 * ci);
+    T w0 = 0, w1[3] = {0, 0, 0}, w4[3] = {0, 0, 0}, fe[6];
     int emask = 0;
-    for (int e = 0; e < ne; e++) {
-      T sign;
-      int k;
-      T val = edge_val(ac + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
-      T jar = val - (carefn[ci] + sign * cbt[3 * ci + k]);
+#pragma unroll
+    for (int e = 0; e < 6; e++) {      // compile-time edge index: every array stays in registers
+      const int k = e >> 1;
       T f = 0;
-      if (jar < 0) {
-        emask |= 1 << e;
-        f = -D * jar;
-        cost += T(0.5) * D * jar * jar;
-        T smu = sign * cmu[3 * ci + k];
-        w[0] += D;                       // W_nn
-        if (dim > 1) { w[1 + k] += D * smu; w[4 + k] += D * smu * smu; }  // W_nk, W_kk
+      if (e < ne) {
+        const T smu = dim == 1 ? T(0) : ((e & 1) ? -cmu[3 * ci + k] : cmu[3 * ci + k]);
+        const T sgn = dim == 1 ? T(0) : ((e & 1) ? T(-1) : T(1));
+        const T jar = (fx.v[0] + smu * fx.v[k + 1]) - (an + sgn * cbt[3 * ci + k]);
+        if (jar < 0) {
+          emask |= 1 << e;
+          f = -D * jar;
+          cost += T(0.5) * D * jar * jar;
+          w0 += D;                                                   // W_nn
+          if (dim > 1) { w1[k] += D * smu; w4[k] += D * smu * smu; }  // W_nk, W_kk
+        }
       }
-      ef[6 * ci + e] = f;
+      fe[e] = f;
     }
-    for (int q = 0; q < 7; q++) W[7 * ci + q] = w[q];
+#pragma unroll
+    for (int e = 0; e < 6; e++) ef[6 * ci + e] = fe[e];
+    T* w = W + 7 * ci;
+    w[0] = w0; w[1] = w1[0]; w[2] = w1[1]; w[3] = w1[2]; w[4] = w4[0]; w[5] = w4[1]; w[6] = w4[2];
     changed |= emask != cmask[ci];
     cmask[ci] = emask;
   }
@@ -404,24 +462,9 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
   if (want_qfc && c.ncon > 0) {
     // frame forces F[ci][4] into O_AV (scratch use), then qfc[j] += sum_r Jr[r][j] F[r]
     T* F = c.template S<O_AV>();
-    _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
-      int dim = c.template I<I_CDIM>()[ci];
-      const T* f = ef + 6 * ci;
-      if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
-      else {
-        T fn = 0;
-        for (int e = 0; e < 2 * (dim - 1); e++) fn += f[e];
-        F[4 * ci] = fn;
-        for (int k = 0; k < 3; k++) F[4 * ci + 1 + k] = (k + 2 <= dim) ? cmu[3 * ci + k] * (f[2 * k] - f[2 * k + 1]) : T(0);
-      }
-    }
+    frame_forces(c, F);
     __syncwarp();
-    const T* JR = c.template G<G_JR>();
-    _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) {
-      T s = 0;
-      for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
-      qfc[j] += s;
-    }
+    add_jt_force(c, F, qfc);
     __syncwarp();
   }
   return warp_sum(cost);
@@ -841,24 +884,9 @@ template <class CX> PHASE_FN void constraint_force(CX& c) {
         if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tendon_coef[2 * id + k]);
       }
   }
-  _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
-    int dim = c.template I<I_CDIM>()[ci];
-    const T* f = ef + 6 * ci;
-    if (dim == 1) { F[4 * ci] = f[0]; F[4 * ci + 1] = F[4 * ci + 2] = F[4 * ci + 3] = 0; }
-    else {
-      T fn = 0;
-      for (int e = 0; e < 2 * (dim - 1); e++) fn += f[e];
-      F[4 * ci] = fn;
-      for (int k = 0; k < 3; k++) F[4 * ci + 1 + k] = (k + 2 <= dim) ? cmu[3 * ci + k] * (f[2 * k] - f[2 * k + 1]) : T(0);
-    }
-  }
+  frame_forces(c, F);
   __syncwarp();
-  const T* JR = c.template G<G_JR>();
-  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) {
-    T s = 0;
-    for (int r = 0; r < 4 * c.ncon; r++) s += JR[r * NVP + j] * F[r];
-    qfc[j] += s;
-  }
+  add_jt_force(c, F, qfc);
   __syncwarp();
 }
 

@@ -484,7 +484,10 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, int n, int lane) {
       Vec4<T> b = ld4(rj + k), a = ld4(r0 + k);
       s0 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
     }
-    for (; k < j; k++) s0 += r0[k] * rj[k];
+    if (k < j) {          // last partial chunk: entries at columns >= j are masked out (j is warp-uniform)
+      Vec4<T> b = ld4(rj + k), a = ld4(r0 + k);
+      s0 += a.v[0] * b.v[0] + (k + 1 < j ? a.v[1] * b.v[1] : T(0)) + (k + 2 < j ? a.v[2] * b.v[2] : T(0));
+    }
     s0 = r0[j] - s0;      // lanes with lane < j read a neighbouring row: harmless, never stored
     T d = __shfl_sync(0xffffffffu, s0, j);
     d = d > tiny<T>() ? d : tiny<T>();
