@@ -175,8 +175,11 @@ __global__ void __launch_bounds__(WPB * 32) collide_kernel(const __grid_constant
 }
 
 // ---------------------------------------------------------------- phase 3: constraint rows + Newton
+#ifndef ADROIT_SOLVE_MINB
+#define ADROIT_SOLVE_MINB 1
+#endif
 template <typename T>
-__global__ void __launch_bounds__(WPB * 32) solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+__global__ void __launch_bounds__(WPB * 32, ADROIT_SOLVE_MINB) solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                           const __grid_constant__ PArgs a) {
   PHASE_PROLOGUE(MapSolve)
   c.ncon = c.gi[GI_NCON];

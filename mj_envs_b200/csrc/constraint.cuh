@@ -669,7 +669,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     if (scale * sqrt(g2) < m.tolerance) break;
     if (refactor) {   // an unchanged active set leaves the Hessian (and its factor) of the previous iteration valid
       build_hessian(c);
-      chol_dense(H, c.template V<V_DINV>(), nv, lane);
+      chol_dense(H, c.template V<V_DINV>(), grad, Mv, nv, lane);   // grad / Mv: free at this point (column broadcast buffers)
     }
     chol_solve(H, c.template V<V_DINV>(), search, nv, lane);
     symv(M, search, Mv, nv, lane);

@@ -428,7 +428,7 @@ template <> DI Vec4<double> ld4<double>(const double* p) {
   Vec4<double> r; r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y; return r;
 }
 template <typename T> DI T rsqrt_t(T d);
-template <> DI float rsqrt_t<float>(float d) { float y = rsqrtf(d); return y * (1.5f - 0.5f * d * y * y); }   // one Newton step: ~1 ulp
+template <> DI float rsqrt_t<float>(float d) { float y = __frsqrt_rn(d); return y * (1.5f - 0.5f * d * y * y); }   // bare MUFU.RSQ (callers clamp d >= 1e-30: no denormal fix-up code) + one Newton step: ~1 ulp
 template <> DI double rsqrt_t<double>(double d) { return 1.0 / sqrt(d); }
 template <typename T> DI T rcp_t(T d);
 template <> DI float rcp_t<float>(float d) { return 1.0f / d; }
@@ -443,6 +443,71 @@ template <typename T> DI void store_vec(T* x, int n, int lane, T x0, T x1) {
   if (lane + 32 < n) x[lane + 32] = x1;
 }
 
+#ifndef ADROIT_BORDERED_SWEEPS
+#define ADROIT_BORDERED_SWEEPS 0   // measured on B200: fewer instructions but a longer dependent chain (border warp sums); 1-2 % slower
+#endif
+#if ADROIT_BORDERED_SWEEPS
+// Triangular sweeps, bordered: the leading min(n,32) block runs on ONE register per lane (x0 = x[lane]); the 1..4 rows
+// beyond lane 31 (n = 33 hammer, 36 relocate) are a border whose entries every lane keeps redundantly in registers --
+// each border row costs one coalesced row read and (forward sweep) one warp sum, instead of doubling the work of every
+// one of the n column steps for the sake of lanes 0..n-33.
+// for k = n-1..0: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[k][i] * xk for i < k      (row k of L is contiguous)
+template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const int nb = n < 32 ? n : 32;
+  if (n > 32) {
+    T xb[4], db[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) { xb[q] = __shfl_sync(FULL, x1, q); db[q] = __shfl_sync(FULL, d1, q); }
+#pragma unroll
+    for (int q = 3; q >= 0; q--) {
+      if (32 + q < n) {                      // warp-uniform
+        const T* row = L + rowoff(32 + q);
+        if (SCALE) xb[q] *= db[q];
+#pragma unroll
+        for (int p = 0; p < q; p++) xb[p] -= row[32 + p] * xb[q];
+        x0 -= row[lane] * xb[q];
+      }
+    }
+    x1 = lane == 0 ? xb[0] : lane == 1 ? xb[1] : lane == 2 ? xb[2] : lane == 3 ? xb[3] : T(0);
+  }
+#pragma unroll 4
+  for (int k = nb - 1; k >= 0; k--) {
+    T xk = __shfl_sync(FULL, SCALE ? x0 * d0 : x0, k);
+    if (SCALE && lane == k) x0 = xk;
+    if (lane < k) x0 -= L[rowoff(k) + lane] * xk;
+  }
+}
+// for k = 0..n-1: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[i][k] * xk for i > k      (column k of L: one row per lane)
+template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const int nb = n < 32 ? n : 32;
+  const T* r0 = L + rowoff(lane);
+#pragma unroll 4
+  for (int k = 0; k < nb; k++) {
+    T xk = __shfl_sync(FULL, SCALE ? x0 * d0 : x0, k);
+    if (SCALE && lane == k) x0 = xk;
+    if (lane > k && lane < nb) x0 -= r0[k] * xk;
+  }
+  if (n > 32) {
+    T xb[4], db[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) { xb[q] = __shfl_sync(FULL, x1, q); db[q] = __shfl_sync(FULL, d1, q); }
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      if (32 + q < n) {                      // warp-uniform
+        const T* row = L + rowoff(32 + q);
+        T s = warp_sum(row[lane] * x0);
+#pragma unroll
+        for (int p = 0; p < q; p++) s += row[32 + p] * xb[p];
+        xb[q] -= s;
+        if (SCALE) xb[q] *= db[q];
+      }
+    }
+    x1 = lane == 0 ? xb[0] : lane == 1 ? xb[1] : lane == 2 ? xb[2] : lane == 3 ? xb[3] : T(0);
+  }
+}
+#else
 // for k = n-1..0: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[k][i] * xk for i < k      (row k of L is contiguous)
 template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
 #pragma unroll 2
@@ -470,12 +535,95 @@ template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1,
   }
 }
 
-// in-place Cholesky A = L L^T; dinv[j] = 1 / L[j][j].  Leading min(n,32) block: left-looking by columns, lane = row,
-// vectorised dot products.  Rows 32..n-1 (n <= 36) are "bordered" on afterwards: each is one forward substitution
+#endif
+
+// in-place Cholesky A = L L^T; dinv[j] = 1 / L[j][j].  Leading min(n,32) block: right-looking, lane = row, the row held
+// in 32 REGISTERS (fully unrolled, compile-time indices): column k is scaled, stored, and broadcast to the warp through
+// a 32-word shared-memory buffer (`col`, two of them alternating: one warp barrier per column), then every lane updates
+// the rest of its row with register FMAs -- ~1.25 instructions per updated entry instead of a dot product re-read from
+// shared memory per entry.  (The kernel is shared-memory-bound at 16 warps/SM, so the registers are free: 128/thread.)
+// Entries right of the diagonal hold don't-care values that never reach a stored result.
+// Rows 32..n-1 (n <= 36) are "bordered" on afterwards: each is one forward substitution
 // against the leading factor plus a few warp-wide dot products, instead of doubling every column step for 1-4 rows.
-template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, int n, int lane) {
+#ifndef ADROIT_REG_CHOL
+#define ADROIT_REG_CHOL 2
+#endif
+template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, int n, int lane) {
   const int nb = n < 32 ? n : 32;
   T* r0 = A + rowoff(lane);
+#if ADROIT_REG_CHOL == 2
+  // rolled by panels of 4 columns: after each panel the register row is rotated by 4, so that the panel code addresses
+  // registers a[0..3] (pivot columns) and a[4..31] (trailing entries) for every panel -- the code footprint of ONE panel
+  // (~4 KB instead of ~30 KB fully unrolled: the solve kernel is instruction-cache bound), the executed work of the
+  // unrolled version (trailing vector groups beyond column 31 are skipped by warp-uniform predicates).
+  T a[32];
+#pragma unroll
+  for (int g = 0; g < 8; g++) {
+    Vec4<T> v = ld4(r0 + 4 * g);
+#pragma unroll
+    for (int q = 0; q < 4; q++) a[4 * g + q] = v.v[q];
+  }
+#pragma unroll 1
+  for (int k0 = 0; k0 < nb; k0 += 4) {
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      const int k = k0 + c;
+      if (k < nb) {                                 // warp-uniform
+        T d = __shfl_sync(0xffffffffu, a[c], k);
+        d = d > tiny<T>() ? d : tiny<T>();
+        const T inv = rsqrt_t(d);
+        const T l = lane > k ? a[c] * inv : (lane == k ? d * inv : T(0));
+        T* cb = (c & 1) ? col1 : col0;
+        cb[lane] = l;
+        if (lane >= k && lane < nb) r0[k] = l;
+        if (lane == k) dinv[k] = inv;
+        __syncwarp();
+#pragma unroll
+        for (int g = 0; g < 8; g++) {
+          if (4 * g + 3 > c && k0 + 4 * g < 32) {   // second condition warp-uniform
+            Vec4<T> cv = ld4(cb + k0 + 4 * g);      // broadcast read of L[k0+4g .. k0+4g+3][k]
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+              if (4 * g + q > c) a[4 * g + q] -= l * cv.v[q];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 28; j++) a[j] = a[j + 4];
+  }
+  __syncwarp();
+#elif ADROIT_REG_CHOL == 1
+  T a[32];
+#pragma unroll
+  for (int g = 0; g < 8; g++) {
+    Vec4<T> v = ld4(r0 + 4 * g);
+#pragma unroll
+    for (int q = 0; q < 4; q++) a[4 * g + q] = v.v[q];
+  }
+#pragma unroll
+  for (int k = 0; k < 32; k++) {
+    if (k < nb) {                                   // warp-uniform
+      T d = __shfl_sync(0xffffffffu, a[k], k);
+      d = d > tiny<T>() ? d : tiny<T>();
+      const T inv = rsqrt_t(d);
+      const T l = lane > k ? a[k] * inv : (lane == k ? d * inv : T(0));   // lanes above the diagonal sit the column out
+      T* cb = (k & 1) ? col1 : col0;
+      cb[lane] = l;
+      if (lane >= k && lane < nb) r0[k] = l;
+      if (lane == k) dinv[k] = inv;
+      __syncwarp();
+#pragma unroll
+      for (int g = (k + 1) >> 2; g < 8; g++) {
+        Vec4<T> cv = ld4(cb + 4 * g);               // broadcast read of L[4g..4g+3][k]
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if (4 * g + q > k) a[4 * g + q] -= l * cv.v[q];
+      }
+    }
+  }
+  __syncwarp();
+#else
   for (int j = 0; j < nb; j++) {
     const T* rj = A + rowoff(j);
     T s0 = 0;
@@ -496,6 +644,7 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, int n, int lane) {
     else if (lane > j && lane < nb) r0[j] = s0 * inv;
     __syncwarp();
   }
+#endif
   for (int r = 32; r < n; r++) {
     T* rr = A + rowoff(r);
     T x = rr[lane], dl = dinv[lane];

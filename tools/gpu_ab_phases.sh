@@ -1,0 +1,5 @@
+# per-phase A/B: every library variant (product + build_ab/*.so) on the workloads in $WORKLOADS, full-length runs
+for lib in mj_envs_b200/libadroit_b200.so build_ab/*.so; do
+  echo "== $lib"
+  ADROIT_B200_LIB=$PWD/$lib bash tools/gpu_phases.sh
+done
