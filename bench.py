@@ -89,8 +89,17 @@ def cpu_reference_run(env_id, sample_envs, steps, warmup, seed=0):
     from oracle.oracle import OracleSim
     task = env_id.split("-")[0]
     cores = len(os.sched_getaffinity(0))
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 for N>1, which would silently turn
+    # the CPU arm into a single-thread run, so it is overridden here and the thread count the runtime reports is recorded
+    os.environ["OMP_NUM_THREADS"] = str(cores)
     sim = OracleSim(task, sample_envs, seed=seed, flags=2)
+    try:
+        import ctypes
+        gomp = ctypes.CDLL("libgomp.so.1")
+        gomp.omp_set_num_threads(cores)
+        cores = int(gomp.omp_get_max_threads())
+    except OSError:
+        pass
     sim.reset()
     rng = np.random.default_rng(seed)
     acts = rng.uniform(-1, 1, (8, sample_envs, sim.nu)).astype(np.float32)
