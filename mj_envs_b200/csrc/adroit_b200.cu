@@ -517,6 +517,11 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
       }
     m.n_tri = (int)tri_ab.size();
     PI(m.ld_start, ld_start); PI(m.ld_pair, ld_pair); PI(m.wl_pair, wl_pair); PI(m.tri_ab, tri_ab);
+    if (maxd > MAXDEPTH) throw std::string("dof ancestor chain longer than dynamics.cuh's MAXDEPTH");
+    std::vector<int> anc_tab((size_t)nv * MAXDEPTH, -1);
+    for (int k = 0; k < nv; k++)
+      for (size_t t = 0; t < anc[k].size(); t++) anc_tab[(size_t)k * MAXDEPTH + t] = anc[k][t];
+    PI(m.dof_depth, depth); PI(m.anc_tab, anc_tab);
     fix.push_back({A.put(lca), (const void**)&m.lca});
   }
   {  // pixel path tables (render.cuh)

@@ -718,30 +718,67 @@ template <typename T> DI void ltdl_solve(const T* L, const T* dinv, T* x, int n,
   store_vec(x, n, lane, x0, x1);
   __syncwarp();
 }
-// M^-1 = W D^-1 W^T with W = L^-1 (unit lower, same ancestor pattern): W by depth levels (wl_pair, levels padded to
-// whole warps), then every entry of M^-1 as a short sum over the common ancestors of its two dofs (lca table).
-template <typename T> PHASE_FN void minv_tree(const DModel<T>& m, const T* L, const T* dinv, T* W, T* Minv, int lane) {
-  for (int p = lane; p < NTRI; p += 32) { W[p] = 0; Minv[p] = 0; }
-  __syncwarp();
-  for (int base = 0; base < m.n_wl; base += 32) {
-    int kj = m.wl_pair[base + lane];
-    if (kj >= 0) {
-      int k = kj & 255, j = kj >> 8;
-      const T* rk = L + rowoff(k);
-      T acc = rk[j];
-      for (int i = m.dof_parent[k]; i > j; i = m.dof_parent[i]) acc += rk[i] * W[tri(i, j)];
-      W[tri(k, j)] = -acc;
+// M^-1 = W D^-1 W^T with W = L^-1 (unit lower, same ancestor pattern as L).
+//  1. W, one ROW per lane, in registers: along the ancestor chain j_0 = parent(k), j_1, ... of dof k
+//        W[k][j_t] = -L[k][j_t] - sum_{s<t} W[k][j_s] L[j_s][j_t]           (from W L = I)
+//     reads only L (shared memory) and the lane's own earlier entries, so the rows need no level ordering and no
+//     barrier; the chain table anc_tab is built on the host.  W then replaces L IN PLACE (unit diagonal stored).
+//  2. every entry of M^-1 as a short sum over the common ancestors of its two dofs (lca table), W and the parent
+//     table read from shared memory: the walk up the chain is a dependent chain of ~25-cycle loads, not L2 round trips.
+// `par` is MAXDEPTH.. >= nv ints of shared scratch.  Pad entries of Minv are never written (zero since allocation).
+constexpr int MAXDEPTH = 14;   // longest dof ancestor chain (relocate: 6 arm + 2 wrist + 5 finger = 13); checked on the host
+template <typename T> PHASE_FN void minv_tree(const DModel<T>& m, T* L, const T* dinv, int* par, T* Minv, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const int nv = m.nv;
+  T w[2][MAXDEPTH];
+#pragma unroll
+  for (int pass = 0; pass < 2; pass++) {
+    const int k = lane + 32 * pass;
+    const bool act = k < nv;
+    if (pass == 1 && nv <= 32) break;                 // warp-uniform
+    if (act) par[k] = m.dof_parent[k];
+    const int d = act ? m.dof_depth[k] : 0;
+    const int maxd = __reduce_max_sync(FULL, d);
+    const int* an = m.anc_tab + (act ? k : 0) * MAXDEPTH;
+    const T* rk = L + rowoff(act ? k : 0);
+    int j[MAXDEPTH], ro[MAXDEPTH];
+#pragma unroll
+    for (int t = 0; t < MAXDEPTH; t++) {
+      j[t] = 0; ro[t] = 0; w[pass][t] = 0;
+      if (t < maxd) {                                 // warp-uniform
+        j[t] = t < d ? an[t] : 0;
+        ro[t] = rowoff(j[t]);
+        T acc = rk[j[t]];
+#pragma unroll
+        for (int q = 0; q < t; q++) acc += w[pass][q] * L[ro[q] + j[t]];
+        w[pass][t] = t < d ? -acc : T(0);
+      }
     }
-    __syncwarp();
   }
+  __syncwarp();
+#pragma unroll
+  for (int pass = 0; pass < 2; pass++) {
+    const int k = lane + 32 * pass;
+    if (pass == 1 && nv <= 32) break;
+    if (k < nv) {
+      const int d = m.dof_depth[k];
+      const int* an = m.anc_tab + k * MAXDEPTH;
+      T* rk = L + rowoff(k);
+#pragma unroll
+      for (int t = 0; t < MAXDEPTH; t++)
+        if (t < d) rk[an[t]] = w[pass][t];
+      rk[k] = T(1);
+    }
+  }
+  __syncwarp();
   for (int p = lane; p < m.n_tri; p += 32) {
     int ab = m.tri_ab[p], a = ab & 255, b = ab >> 8;   // a >= b
-    int k = m.lca[a * m.nv + b];
+    int k = m.lca[a * nv + b];
+    const T *ra = L + rowoff(a), *rb = L + rowoff(b);
     T s = 0;
     while (k != 255) {
-      T wa = k == a ? T(1) : W[tri(a, k)], wb = k == b ? T(1) : W[tri(b, k)];
-      s += wa * wb * dinv[k];
-      int pk = m.dof_parent[k];
+      s += ra[k] * rb[k] * dinv[k];
+      int pk = par[k];
       k = pk < 0 ? 255 : pk;
     }
     Minv[tri(a, b)] = s;
@@ -803,7 +840,7 @@ template <class CX> PHASE_FN void smooth_dynamics(CX& c, bool need_minv) {
   __syncwarp();
   ltdl_factor(m, H, c.template V<V_DINV>(), c.lane);
   ltdl_solve(H, c.template V<V_DINV>(), qas, m.nv, c.lane);
-  if (need_minv) minv_tree(m, H, c.template V<V_DINV>(), c.template G<G_LINV>(), c.template G<G_MINV>(), c.lane);
+  if (need_minv) minv_tree(m, H, c.template V<V_DINV>(), reinterpret_cast<int*>(act), c.template G<G_MINV>(), c.lane);   // act (V_T2): free by now
 }
 
 }  // namespace adroit

@@ -111,6 +111,7 @@ template <typename T> struct DModel {
   const int* act_dof;
   // tree-sparse factorisation tables (host-built from dof_parent, see fill_model)
   const int *ld_start, *ld_pair, *wl_pair, *tri_ab;   // [nv+1], [..] i|j<<8, [..] k|j<<8, [ntri_real] a|b<<8
+  const int *dof_depth, *anc_tab;                    // [nv] number of proper ancestor dofs, [nv][MAXDEPTH] the chain, nearest first (-1 padded)
   const unsigned char* lca;                          // [nv*nv] deepest common ancestor-or-self dof, 255 = none
   const T *act_ctrlrange, *act_gain, *act_bias;
   const int* render_int;                             // [nrender][4] type, body, par offset of the local pos (-1), is_site
