@@ -298,6 +298,10 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
   __syncwarp();
 }
 
+#ifndef ADROIT_CFM_UNROLL
+#define ADROIT_CFM_UNROLL 2
+#endif
+constexpr int CFM_UNROLL = ADROIT_CFM_UNROLL;
 // J_r . x for a simple row
 template <typename T> DI T simple_dot(const DModel<T>& m, int info, const T* x) {
   int kind = info & 3, id = (info >> 2) & 1023, up = (info >> 12) & 1;
@@ -318,7 +322,7 @@ template <class CX> SUB_FN void contact_frame_mul(CX& c, const typename CX::real
   const int nv = c.m.nv, lane = c.lane;
   T x0, x1;
   load_vec(x, nv, lane, x0, x1);
-#pragma unroll 2
+#pragma unroll(CFM_UNROLL)
   for (int ci = 0; ci < c.ncon; ci++) {
     const T* J = JR + 4 * ci * NVP;
     T v[4];
@@ -367,7 +371,7 @@ template <class CX> DI void add_jt_force(CX& c, const typename CX::real* F, type
   const T* JR = c.template G<G_JR>();
   const int nv = c.m.nv, lane = c.lane;
   T a0 = 0, a1 = 0;
-#pragma unroll 2
+#pragma unroll(CFM_UNROLL)
   for (int ci = 0; ci < c.ncon; ci++) {
     Vec4<T> f = ld4(F + 4 * ci);
     if (f.v[0] == 0 && f.v[1] == 0 && f.v[2] == 0 && f.v[3] == 0) continue;   // warp-uniform (shared-memory values)
