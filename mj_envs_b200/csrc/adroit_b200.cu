@@ -55,18 +55,28 @@ struct MapCollide {
   static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}};
   static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV, 0}};
 };
-struct MapSolve {
+// The solve kernel comes in two size classes (MC = contact capacity of the shared-memory tables): envs with at most
+// MAXCON_S contacts -- all of them in random play, nearly all under the DAPG policies -- run in the small class, whose
+// shared-memory slice is 11.4 KB per env instead of 13.5 KB: 5 blocks (20 envs) per SM instead of 4 (16).  Each class is
+// its own launch over the same env range; a warp whose env belongs to the other class exits before staging anything.
+#ifndef ADROIT_MAXCON_S
+#define ADROIT_MAXCON_S 16
+#endif
+constexpr int MAXCON_S = ADROIT_MAXCON_S;
+template <int MC> struct MapSolveT {
   static constexpr int NT = 24, NI = 5;
   static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_MA, R_ZERO),
                                  VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_QFC, R_ZERO | R_OUT), VR(V_DINV, R_ZERO),
                                  Reg{O_M, NTRI, R_IN},   // (A/B: reading M from L1/L2 instead costs 30 %)
                                  Reg{O_H, NTRI, 0},
                                  Reg{O_SD, MAXSIMPLE, R_OUT}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
-                                 Reg{O_AC, CROWS, 0}, Reg{O_AV, CROWS, 0}, Reg{O_CD, MAXCON, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
-                                 Reg{O_CAREFN, MAXCON, 0}, Reg{O_CBT, MAXCON * 3, R_OUT}, Reg{O_EF, MAXCON * 6, R_OUT}, Reg{O_W, MAXCON * 7, 0}};
-  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MAXCON, R_IN}, Reg{I_CB1, MAXCON, R_IN}, Reg{I_CB2, MAXCON, R_IN},
-                                 Reg{I_CMASK, MAXCON, 0}};
+                                 Reg{O_AC, MC * 4, 0}, Reg{O_AV, MC * 4, 0}, Reg{O_CD, MC, 0}, Reg{O_CMU, MC * 3, R_IN},
+                                 Reg{O_CAREFN, MC, 0}, Reg{O_CBT, MC * 3, R_OUT}, Reg{O_EF, MC * 6, R_OUT}, Reg{O_W, MC * 7, 0}};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MC, R_IN}, Reg{I_CB1, MC, R_IN}, Reg{I_CB2, MC, R_IN},
+                                 Reg{I_CMASK, MC, 0}};
 };
+using MapSolve = MapSolveT<MAXCON>;
+using MapSolveS = MapSolveT<MAXCON_S>;
 // M^-1 is staged (read-only) for the noslip sweeps; the same shared-memory region then holds the (M + hB) factor
 struct MapFinish {
   static constexpr int NT = 20, NI = 3;
@@ -175,13 +185,18 @@ __global__ void __launch_bounds__(WPB * 32) collide_kernel(const __grid_constant
 }
 
 // ---------------------------------------------------------------- phase 3: constraint rows + Newton
-#ifndef ADROIT_SOLVE_MINB
-#define ADROIT_SOLVE_MINB 1
-#endif
-template <typename T>
-__global__ void __launch_bounds__(WPB * 32, ADROIT_SOLVE_MINB) solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
-                                                          const __grid_constant__ PArgs a) {
-  PHASE_PROLOGUE(MapSolve)
+// MC = MAXCON_S: envs with ncon <= MAXCON_S; MC = MAXCON: the others (see MapSolveT).  The small class is compiled for
+// 5 blocks per SM (<= 102 registers), which its shared-memory slice allows.
+template <typename T, int MC>
+__global__ void __launch_bounds__(WPB * 32, (MC < MAXCON && sizeof(T) == 4) ? 5 : 1)
+    solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, const __grid_constant__ PArgs a) {
+  if (MAXCON_S < MAXCON) {
+    const int env_ = a.env0 + blockIdx.x * WPB + (threadIdx.x >> 5);
+    if (env_ >= a.env1) return;
+    const bool small = st.ctxi[(size_t)env_ * CTX_I + SM_I + GI_NCON] <= MAXCON_S;
+    if (small != (MC < MAXCON)) return;
+  }
+  PHASE_PROLOGUE(MapSolveT<MC>)
   c.ncon = c.gi[GI_NCON];
   make_constraint(c, st.overflow);
   newton(c);
@@ -621,7 +636,8 @@ int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const D
 template <typename T> int configure_kernels() {
   CK(cudaFuncSetAttribute(smooth_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSmooth>())));
   CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapCollide>())));
-  CK(cudaFuncSetAttribute(solve_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSolve>())));
+  CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSolve>())));
+  if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSolveS>())));
   CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapFinish>())));
   return 0;
 }
@@ -630,7 +646,8 @@ template <typename T> int configure_kernels() {
 template <typename T> int forward_pass(adroit_sim* s, const DModel<T>& m, const DState<T>& st, PArgs a, cudaStream_t stream) {
   if (launch_phase<T, MapSmooth>(s, 0, smooth_kernel<T>, m, st, a, stream)) return 1;
   if (launch_phase<T, MapCollide>(s, 1, collide_kernel<T>, m, st, a, stream)) return 1;
-  if (launch_phase<T, MapSolve>(s, 2, solve_kernel<T>, m, st, a, stream)) return 1;
+  if (MAXCON_S < MAXCON && launch_phase<T, MapSolveS>(s, 2, solve_kernel<T, MAXCON_S>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapSolve>(s, 2, solve_kernel<T, MAXCON>, m, st, a, stream)) return 1;
   if (launch_phase<T, MapFinish>(s, 3, finish_kernel<T>, m, st, a, stream)) return 1;
   return 0;
 }
