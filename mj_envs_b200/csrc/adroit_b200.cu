@@ -531,6 +531,12 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
         lca[(size_t)a * nv + b] = v; lca[(size_t)b * nv + a] = v;
       }
     m.n_tri = (int)tri_ab.size();
+    std::vector<int> tri_abk(tri_ab.size());
+    for (size_t q = 0; q < tri_ab.size(); q++) {
+      int a = tri_ab[q] & 255, b = tri_ab[q] >> 8;
+      tri_abk[q] = a | (b << 8) | ((int)lca[(size_t)a * nv + b] << 16);
+    }
+    PI(m.tri_abk, tri_abk);
     PI(m.ld_start, ld_start); PI(m.ld_pair, ld_pair); PI(m.wl_pair, wl_pair); PI(m.tri_ab, tri_ab);
     if (maxd > MAXDEPTH) throw std::string("dof ancestor chain longer than dynamics.cuh's MAXDEPTH");
     std::vector<int> anc_tab((size_t)nv * MAXDEPTH, -1);

@@ -771,9 +771,13 @@ template <typename T> PHASE_FN void minv_tree(const DModel<T>& m, T* L, const T*
     }
   }
   __syncwarp();
+  // (a, b, lca(a,b)) packed in one table word, fetched one pass ahead: the model-table load is off the dependent chain
+  int nxt = lane < m.n_tri ? m.tri_abk[lane] : 0;
   for (int p = lane; p < m.n_tri; p += 32) {
-    int ab = m.tri_ab[p], a = ab & 255, b = ab >> 8;   // a >= b
-    int k = m.lca[a * nv + b];
+    const int abk = nxt;
+    if (p + 32 < m.n_tri) nxt = m.tri_abk[p + 32];
+    const int a = abk & 255, b = (abk >> 8) & 255;     // a >= b
+    int k = (abk >> 16) & 255;
     const T *ra = L + rowoff(a), *rb = L + rowoff(b);
     T s = 0;
     while (k != 255) {
