@@ -316,7 +316,12 @@ def main():
     traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_path):
         try:
-            line["roofline"]["traffic"] = json.load(open(traffic_path)).get(f"{env_id}:{n_envs}")
+            # measured DRAM bytes of one launch of the dominant kernel (ncu --set full, profiles/), scaled from the
+            # captured sub-batch launch to this launch's env count -- per launch, like `achieved`
+            t = json.load(open(traffic_path)).get(env_id)
+            if t and t.get("kernel") == names[dom]:
+                line["roofline"]["traffic"] = t["dram_bytes_per_env_launch"] * n_envs
+                line["roofline"]["traffic_source"] = t["source"]
         except Exception:
             pass
     if rank == 0 and world == 1 and args.also:

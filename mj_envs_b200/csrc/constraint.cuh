@@ -250,50 +250,86 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
   const T *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>();
   T *JR = c.template G<G_JR>();
   T *cD = c.template S<O_CD>(), *cmu = c.template S<O_CMU>(), *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>(), *ef = c.template S<O_EF>();
+  // Everything that does not depend on the contact is read once, up front: the lane's two dofs (lane, lane + 32) with
+  // their joint type, axis, anchor and velocity, and the dof masks of every contact's two bodies (lane = contact).  The
+  // contact record of the NEXT contact is fetched while the current one is worked on, so that no model-table or
+  // context load sits on the dependent chain of the serial loop over contacts.
+  const T* CON = c.template G<G_CON>();
+  T *av = c.template S<O_AV>();      // scratch until the first Newton iteration: frame velocity J v of every contact
+  int jt[2];
+  T ax[2][3], an[2][3], qv[2];
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const int j = c.lane + 32 * h;
+    const bool ok = j < m.nv;
+    jt[h] = ok ? m.jnt_type[j] : -1;
+#pragma unroll
+    for (int i = 0; i < 3; i++) { ax[h][i] = ok ? xaxis[3 * j + i] : T(0); an[h][i] = ok ? xanc[3 * j + i] : T(0); }
+    qv[h] = ok ? qvel[j] : T(0);
+  }
+  unsigned long long mym1 = 0, mym2 = 0;
+  if (c.lane < c.ncon) { mym1 = m.body_dofmask[c.template I<I_CB1>()[c.lane]]; mym2 = m.body_dofmask[c.template I<I_CB2>()[c.lane]]; }
+  T Cn[12];
+  if (c.ncon > 0) {
+#pragma unroll
+    for (int i = 0; i < 12; i++) Cn[i] = CON[1 + i];
+  }
   for (int ci = 0; ci < c.ncon; ci++) {
-    const T* C = c.template G<G_CON>() + 16 * ci;
-    int b1 = c.template I<I_CB1>()[ci], b2 = c.template I<I_CB2>()[ci], dim = c.template I<I_CDIM>()[ci];
-    unsigned long long m1 = m.body_dofmask[b1], m2 = m.body_dofmask[b2];
+    T C[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) C[i] = Cn[i];     // C[i] = record[1 + i]: position (3), frame rows (9)
+    if (ci + 1 < c.ncon) {
+#pragma unroll
+      for (int i = 0; i < 12; i++) Cn[i] = CON[16 * (ci + 1) + 1 + i];
+    }
+    const unsigned long long m1 = __shfl_sync(0xffffffffu, mym1, ci), m2 = __shfl_sync(0xffffffffu, mym2, ci);
     T vsum[4] = {0, 0, 0, 0};
-    _Pragma("unroll 1") for (int j = c.lane; j < NVP; j += 32) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int j = c.lane + 32 * h;
+      if (h == 1 && c.lane >= NVP - 32) break;
       T row[4] = {0, 0, 0, 0};
-      if (j < m.nv) {
+      if (jt[h] >= 0) {
         int sg = (int)((m2 >> j) & 1ull) - (int)((m1 >> j) & 1ull);
         if (sg != 0) {
-          const T* a = xaxis + 3 * j;
+          const T* a = ax[h];
           T jp[3], jr[3] = {0, 0, 0};
-          if (m.jnt_type[j] == J_SLIDE) { jp[0] = a[0]; jp[1] = a[1]; jp[2] = a[2]; }
+          if (jt[h] == J_SLIDE) { jp[0] = a[0]; jp[1] = a[1]; jp[2] = a[2]; }
           else {
-            T r[3] = {C[1] - xanc[3 * j], C[2] - xanc[3 * j + 1], C[3] - xanc[3 * j + 2]};
+            T r[3] = {C[0] - an[h][0], C[1] - an[h][1], C[2] - an[h][2]};
             cross3(jp, a, r);
             jr[0] = a[0]; jr[1] = a[1]; jr[2] = a[2];
           }
           T s = (T)sg;
-          row[0] = s * (C[4] * jp[0] + C[5] * jp[1] + C[6] * jp[2]);
-          row[1] = s * (C[7] * jp[0] + C[8] * jp[1] + C[9] * jp[2]);
-          row[2] = s * (C[10] * jp[0] + C[11] * jp[1] + C[12] * jp[2]);
-          row[3] = s * (C[4] * jr[0] + C[5] * jr[1] + C[6] * jr[2]);
-          for (int a4 = 0; a4 < 4; a4++) vsum[a4] += row[a4] * qvel[j];
+          row[0] = s * (C[3] * jp[0] + C[4] * jp[1] + C[5] * jp[2]);
+          row[1] = s * (C[6] * jp[0] + C[7] * jp[1] + C[8] * jp[2]);
+          row[2] = s * (C[9] * jp[0] + C[10] * jp[1] + C[11] * jp[2]);
+          row[3] = s * (C[3] * jr[0] + C[4] * jr[1] + C[5] * jr[2]);
+#pragma unroll
+          for (int a4 = 0; a4 < 4; a4++) vsum[a4] += row[a4] * qv[h];
         }
       }
+#pragma unroll
       for (int a4 = 0; a4 < 4; a4++) JR[(4 * ci + a4) * NVP + j] = row[a4];
     }
-    {
-      T t = warp_sum4(vsum[0], vsum[1], vsum[2], vsum[3], c.lane);
-      for (int a4 = 0; a4 < 4; a4++) vsum[a4] = __shfl_sync(0xffffffffu, t, 8 * a4);
-    }
-    if (c.lane == 0) {
-      T dist = C[0], mg = C[13], imp = impedance(m, dist, mg);
-      T tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
-      T mu0 = cmu[3 * ci];
-      T diag = dim == 1 ? tran : tran + mu0 * mu0 * tran;
-      T R = tmax(T(1e-15), (1 - imp) * diag / imp);
-      if (dim > 1) { T mu = mu0 * sqrt(T(1) / m.impratio); R = 2 * mu * mu * R; }
-      cD[ci] = T(1) / R;
-      carefn[ci] = -B * vsum[0] - K * imp * (dist - mg);
-      for (int k = 0; k < 3; k++) cbt[3 * ci + k] = (k + 2 <= dim) ? -B * cmu[3 * ci + k] * vsum[k + 1] : T(0);
-      for (int e = 0; e < 6; e++) ef[6 * ci + e] = 0;
-    }
+    T t = warp_sum4(vsum[0], vsum[1], vsum[2], vsum[3], c.lane);
+    if ((c.lane & 7) == 0) av[4 * ci + (c.lane >> 3)] = t;
+  }
+  __syncwarp();
+  // per-contact scalars, lane = contact
+  _Pragma("unroll 1") for (int ci = c.lane; ci < c.ncon; ci += 32) {
+    const T* C = CON + 16 * ci;
+    const int b1 = c.template I<I_CB1>()[ci], b2 = c.template I<I_CB2>()[ci], dim = c.template I<I_CDIM>()[ci];
+    T dist = C[0], mg = C[13], imp = impedance(m, dist, mg);
+    T tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
+    T mu0 = cmu[3 * ci];
+    T diag = dim == 1 ? tran : tran + mu0 * mu0 * tran;
+    T R = tmax(T(1e-15), (1 - imp) * diag / imp);
+    if (dim > 1) { T mu = mu0 * sqrt(T(1) / m.impratio); R = 2 * mu * mu * R; }
+    cD[ci] = T(1) / R;
+    carefn[ci] = -B * av[4 * ci] - K * imp * (dist - mg);
+    for (int k = 0; k < 3; k++) cbt[3 * ci + k] = (k + 2 <= dim) ? -B * cmu[3 * ci + k] * av[4 * ci + k + 1] : T(0);
+    for (int e = 0; e < 6; e++) ef[6 * ci + e] = 0;
   }
   __syncwarp();
 }

@@ -26,8 +26,15 @@ for f in glob.glob(os.path.join(src, f"{tag}_*.ncu-rep")):
         p = l.split()
         if "dram__bytes_read.sum" in l: rd = float(p[1]) * (1e6 if p[2].startswith("M") else 1e9 if p[2].startswith("G") else 1e3 if p[2].startswith("K") else 1)
         if "dram__bytes_write.sum" in l: wr = float(p[1]) * (1e6 if p[2].startswith("M") else 1e9 if p[2].startswith("G") else 1e3 if p[2].startswith("K") else 1)
-    if rd is not None and "solve" in name: traffic["hammer-v0:8192"] = rd + wr
-    lines.append(f"* `{name}.summary.txt`: `ncu --set full` of one launch (hammer-v0 x 8192, late episode)")
+    grid = None
+    for l in out.splitlines():
+        if "launch__grid_size" in l: grid = float(l.split()[1])
+    task = name.rsplit("_", 1)[-1]
+    if rd is not None and grid and "solve" in name:
+        # DRAM bytes per env of ONE launch of the dominant kernel (4 envs per block); bench.py scales it to its launch size
+        traffic[f"{task}-v0"] = {"dram_bytes_per_env_launch": (rd + wr) / (grid * 4), "kernel": "solve_kernel", "envs_in_captured_launch": int(grid * 4),
+                                 "source": f"profiles/{name}.summary.txt"}
+    lines.append(f"* `{name}.summary.txt`: `ncu --set full` of one launch ({task}-v0, late episode)")
 for f, tool in ((f"{tag}_hammer_kernels.csv", "ncu_kernels.py"), (f"{tag}_launches.csv", "ncu_launches.py")):
     p = os.path.join(src, f)
     if os.path.exists(p):
@@ -41,7 +48,9 @@ tp = os.path.join(dst, "traffic.json")
 old = json.load(open(tp)) if os.path.exists(tp) else {}
 if traffic:
     old.update(traffic)
-    old["_source"] = "dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel (solve_kernel), ncu --set full"
+    old = {k: v for k, v in old.items() if isinstance(v, dict)}
+    old.update(traffic)
+    old["_source"] = "dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel (solve_kernel), ncu --set full, per env of that launch"
     json.dump(old, open(tp, "w"))
 open(os.path.join(dst, "README.md"), "w").write("\n".join(lines) + "\n")
 print("\n".join(lines))
