@@ -510,7 +510,10 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
     for (int k = 0; k < nv; k++) {
       ld_start[k] = (int)ld_pair.size();
       for (size_t a = 0; a < anc[k].size(); a++)
-        for (size_t b = a; b < anc[k].size(); b++) ld_pair.push_back(anc[k][a] | (anc[k][b] << 8));   // i >= j
+        for (size_t b = a; b < anc[k].size(); b++) {                                                    // i >= j
+          const int i = anc[k][a], j = anc[k][b], g = i >> 2;
+          ld_pair.push_back((4 * (g + 1) * (2 * g + (i & 3)) + j) | (i << 10) | (j << 16));             // model.cuh tri(i, j)
+        }
     }
     ld_start[nv] = (int)ld_pair.size();
     int maxd = 0;

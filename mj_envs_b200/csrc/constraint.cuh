@@ -356,18 +356,25 @@ template <class CX> SUB_FN void contact_frame_mul(CX& c, const typename CX::real
   using T = typename CX::real;
   const T* JR = c.template G<G_JR>();
   const int nv = c.m.nv, lane = c.lane;
+  const bool hi = nv > 32 && lane < NVP - 32;
   T x0, x1;
   load_vec(x, nv, lane, x0, x1);
-#pragma unroll(CFM_UNROLL)
-  for (int ci = 0; ci < c.ncon; ci++) {
+  // the rows of the NEXT contact are in flight while the current one is reduced (J lives in L2)
+  T jn[8];
+  auto fetch = [&](int ci) {
     const T* J = JR + 4 * ci * NVP;
+#pragma unroll
+    for (int a = 0; a < 4; a++) jn[a] = J[a * NVP + lane];              // pad columns of J are zero
+#pragma unroll
+    for (int a = 0; a < 4; a++) jn[4 + a] = hi ? J[a * NVP + 32 + lane] : T(0);
+  };
+  if (c.ncon > 0) fetch(0);
+#pragma unroll 1
+  for (int ci = 0; ci < c.ncon; ci++) {
     T v[4];
 #pragma unroll
-    for (int a = 0; a < 4; a++) v[a] = J[a * NVP + lane] * x0;          // pad columns of J are zero
-    if (nv > 32 && lane < NVP - 32) {
-#pragma unroll
-      for (int a = 0; a < 4; a++) v[a] += J[a * NVP + 32 + lane] * x1;
-    }
+    for (int a = 0; a < 4; a++) v[a] = jn[a] * x0 + jn[4 + a] * x1;
+    if (ci + 1 < c.ncon) fetch(ci + 1);
     T t = warp_sum4(v[0], v[1], v[2], v[3], lane);
     if ((lane & 7) == 0) out[4 * ci + (lane >> 3)] = t;
   }

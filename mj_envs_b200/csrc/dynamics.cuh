@@ -690,15 +690,25 @@ template <typename T> DI void chol_solve(const T* L, const T* dinv, T* x, int n,
 // ld_start / ld_pair is built on the host.  On return: strict lower part = L, diagonal = D, dinv = 1/D.
 template <typename T> PHASE_FN void ltdl_factor(const DModel<T>& m, T* A, T* dinv, int lane) {
   const int n = m.nv;
+  // schedule words (host-built): packed offset of A[i][j] | i << 10 | j << 16.  The first pass of the NEXT pivot's
+  // words is fetched while the current pivot is eliminated: no model-table load on the chain of the 33 serial pivots.
+  int beg = m.ld_start[n - 1], end = m.ld_start[n];
+  int nxt = beg + lane < end ? m.ld_pair[beg + lane] : 0;
   for (int k = n - 1; k >= 0; k--) {
+    const int cb = beg, ce = end, cur = nxt;
+    if (k > 0) {
+      end = beg;
+      beg = m.ld_start[k - 1];
+      nxt = beg + lane < end ? m.ld_pair[beg + lane] : 0;
+    }
     const T* rk = A + rowoff(k);
     T dk = rk[k];
     dk = dk > tiny<T>() ? dk : tiny<T>();
     T inv = rcp_t(dk);
-    int beg = m.ld_start[k], end = m.ld_start[k + 1];
-    for (int p = beg + lane; p < end; p += 32) {
-      int ij = m.ld_pair[p], i = ij & 255, j = ij >> 8;
-      A[tri(i, j)] -= rk[i] * rk[j] * inv;
+    for (int p = cb + lane; p < ce; p += 32) {
+      const int w = p == cb + lane ? cur : m.ld_pair[p];
+      const int off = w & 1023, i = (w >> 10) & 63, j = (w >> 16) & 63;
+      A[off] -= rk[i] * rk[j] * inv;
     }
     __syncwarp();
     // row k: L[k][i] = A[k][i] / D[k] for every i < k (entries outside the ancestor pattern are zero and stay zero)

@@ -110,7 +110,7 @@ template <typename T> struct DModel {
   const T *tendon_coef, *tendon_range, *tendon_margin, *tendon_invweight0;
   const int* act_dof;
   // tree-sparse factorisation tables (host-built from dof_parent, see fill_model)
-  const int *ld_start, *ld_pair, *wl_pair, *tri_ab;   // [nv+1], [..] i|j<<8, [..] k|j<<8, [ntri_real] a|b<<8
+  const int *ld_start, *ld_pair, *wl_pair, *tri_ab;   // [nv+1], [..] tri(i,j)|i<<10|j<<16, [..] k|j<<8, [ntri_real] a|b<<8
   const int *tri_abk;                                // [n_tri] a | b<<8 | lca(a,b)<<16 (255 = none), a >= b
   const int *dof_depth, *anc_tab;                    // [nv] number of proper ancestor dofs, [nv][MAXDEPTH] the chain, nearest first (-1 padded)
   const unsigned char* lca;                          // [nv*nv] deepest common ancestor-or-self dof, 255 = none
