@@ -340,7 +340,10 @@ template <class CX> PHASE_FN void rne_bias(CX& c) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
   const T *xpos = c.template S<O_XPOS>(), *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>(), *qvel = c.template V<V_QVEL>();
-  T *vel = c.template G<G_VEL>(), *acc = c.template G<G_ACC>(), *frc = c.template G<G_FRC>();
+  // body velocities / accelerations / forces live in the shared-memory region of the (not yet built) factor O_H: the
+  // level loops read what the previous level wrote, and from the context block that was an L2 round trip per level
+  static_assert(18 * NBP <= NTRI, "rne scratch is aliased onto O_H");
+  T *vel = c.template S<O_H>(), *acc = vel + 6 * NBP, *frc = vel + 12 * NBP;
   if (c.lane == 0) {
     for (int i = 0; i < 6; i++) { vel[i] = 0; frc[i] = 0; }
     acc[0] = acc[1] = acc[2] = 0;
@@ -352,6 +355,8 @@ template <class CX> PHASE_FN void rne_bias(CX& c) {
     for (int idx = beg + c.lane; idx < end; idx += 32) {
       int b = m.level_body[idx], p = m.body_parent[b];
       const T* O = xpos + 3 * b;
+      T Ib[10];                                                  // single-body inertia (context block): fetched first
+      for (int e = 0; e < 10; e++) Ib[e] = c.template G<G_CIN>()[10 * b + e];
       T r[3] = {O[0] - xpos[3 * p], O[1] - xpos[3 * p + 1], O[2] - xpos[3 * p + 2]};
       T v[6], a[6], t[3];
       for (int i = 0; i < 6; i++) { v[i] = vel[6 * p + i]; a[i] = acc[6 * p + i]; }
@@ -373,7 +378,7 @@ template <class CX> PHASE_FN void rne_bias(CX& c) {
         for (int i = 0; i < 6; i++) v[i] += vj[i];
       }
       for (int i = 0; i < 6; i++) { vel[6 * b + i] = v[i]; acc[6 * b + i] = a[i]; }
-      const T* I = c.template G<G_CIN>() + 10 * b;
+      const T* I = Ib;
       T Ia[6], Iv[6], f[6], u[3];
       inert_mul(Ia, I, a);
       inert_mul(Iv, I, v);
