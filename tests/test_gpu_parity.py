@@ -168,3 +168,41 @@ def test_errors_are_reported_not_swallowed():
     h = C.c_void_p()
     assert abi.create(b"garbage-blob-----", 16, 4, 0, 0, 0, 0, C.byref(h)) != 0
     assert b"blob" in abi.last_error()
+
+
+@pytest.mark.parametrize("task,scale", [("hammer", 0.35), ("relocate", 0.29)])
+def test_fp64_many_contact_states_cover_both_solve_size_classes(task, scale):
+    """The solve kernel runs in two size classes (<= 16 contacts / up to 32, adroit_b200.cu MapSolveT).  Random play never
+    leaves the small class, so this test builds states with curled, self-colliding fingers: some envs carry 17..32
+    contacts and go through the big class; every env must still match the oracle from identical states."""
+    torch, AdroitVecEnv, OracleSim = _mods()
+    n = 128
+    env = AdroitVecEnv(f"{task}-v0", n, seed=3, fp64=True)
+    ora = OracleSim(task, n, seed=3)
+    env.reset(); ora.reset()
+    q, v, p = ora.get_state()
+    rng = np.random.default_rng(1)
+    q = q.copy()
+    q[:, :ora.nv - 6] += rng.uniform(-0.3, 0.9, (n, ora.nv - 6)) * scale   # scales chosen with the oracle: 17..21 contacts at most
+    ora.set_state(q, np.zeros_like(v), p)
+    L = env.debug_layout()
+    big = 0
+    for t in range(3):
+        q, v, p = ora.get_state()
+        env._set_raw_state(q, v, p)
+        env.set_warmstart(ora.get_warmstart())
+        a = rng.uniform(-1, 1, (n, env.nu)).astype(np.float32)
+        ora.step(a)
+        env.step(torch.from_numpy(a))
+        _, ncon_o, _, _ = ora.solver()
+        gi = np.zeros((n, L["GI_TOTAL"]), dtype=np.int32)
+        env.abi.lib.adroit_debug_iscratch(env._h, gi.ctypes.data, None)
+        ncon_g = gi[:, 0]
+        assert env.overflow().sum() == 0        # the CUDA path keeps 32 contacts per env; beyond that it only counts
+        assert np.array_equal(ncon_g, ncon_o)
+        big += int((ncon_g > 16).sum())
+        gq, gv, _ = env._raw_state()
+        nq, nv_, _ = ora.get_state()
+        assert _rel(gq, nq).max() < 1e-9 and _rel(gv, nv_).max() < 1e-8, (t, _rel(gq, nq).max(), _rel(gv, nv_).max())
+    assert big > 0, "no env exercised the 32-contact size class"
+    env.close()
