@@ -433,10 +433,18 @@ template <> DI Vec4<double> ld4<double>(const double* p) {
   Vec4<double> r; r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y; return r;
 }
 template <typename T> DI T rsqrt_t(T d);
-template <> DI float rsqrt_t<float>(float d) { float y = __frsqrt_rn(d); return y * (1.5f - 0.5f * d * y * y); }   // bare MUFU.RSQ (callers clamp d >= 1e-30: no denormal fix-up code) + one Newton step: ~1 ulp
+template <> DI float rsqrt_t<float>(float d) {   // bare MUFU.RSQ (callers clamp d >= 1e-30: no denormal fix-up) + one Newton step: ~1 ulp
+  float y;                                       // (__frsqrt_rn is the correctly-rounded ~20-instruction sequence, rsqrtf adds range fix-ups)
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(d));
+  return y * (1.5f - 0.5f * d * y * y);
+}
 template <> DI double rsqrt_t<double>(double d) { return 1.0 / sqrt(d); }
 template <typename T> DI T rcp_t(T d);
-template <> DI float rcp_t<float>(float d) { return 1.0f / d; }
+template <> DI float rcp_t<float>(float d) {     // MUFU.RCP + one Newton step (callers clamp d >= 1e-30); ~1 ulp, a third of the IEEE division sequence
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(d));
+  return y * (2.0f - d * y);
+}
 template <> DI double rcp_t<double>(double d) { return 1.0 / d; }
 
 template <typename T> DI void load_vec(const T* x, int n, int lane, T& x0, T& x1) {
