@@ -781,6 +781,10 @@ template <class CX> PHASE_FN void newton(CX& c) {
 //     round per CHANGED row instead of one per row (saturated friction rows -- moving joints -- never change);
 //   * contact tangents: a compact list of tangent rows; the Jacobian row and its M^-1 image are prefetched one
 //     tangent ahead, so the global loads are off the dependent chain  dot -> warp sum -> clamp -> update.
+// a / b on the dependent Gauss-Seidel chain: fp32 multiplies by the reciprocal prepared off the chain (MUFU.RCP + one
+// Newton step, ~1 ulp; the IEEE division is a ~10-instruction dependent sequence), fp64 divides
+DI float quot(float a, float, float rb) { return a * rb; }
+DI double quot(double a, double b, double) { return a / b; }
 template <class CX> PHASE_FN void noslip(CX& c) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
@@ -821,7 +825,7 @@ template <class CX> PHASE_FN void noslip(CX& c) {
   load_vec(qas, nv, lane, q0, q1);
   bool val[2];
   int dj[2];
-  T qd[2], sa[2], Aii[2], fl[2], f[2];
+  T qd[2], sa[2], Aii[2], rA[2], fl[2], f[2];   // rA = 1 / Aii (fp32: the Gauss-Seidel chain multiplies, see quot())
 #pragma unroll
   for (int s = 0; s < 2; s++) {
     int r = lane + 32 * s;
@@ -831,6 +835,7 @@ template <class CX> PHASE_FN void noslip(CX& c) {
     qd[s] = qas[dj[s]];
     sa[s] = val[s] ? saref[r] : T(0);
     Aii[s] = Minv[tri(dj[s], dj[s])];
+    rA[s] = rcp_t(Aii[s] > tiny<T>() ? Aii[s] : tiny<T>());
     fl[s] = val[s] ? sfl[r] : T(0);
     f[s] = val[s] ? sforce[r] : T(0);
   }
@@ -852,7 +857,7 @@ template <class CX> PHASE_FN void noslip(CX& c) {
           ud = dj[s] < 32 ? a : b;
         }
         res[s] = ud + qd[s] - sa[s];
-        fn[s] = tclamp(f[s] - res[s] / Aii[s], -fl[s], fl[s]);
+        fn[s] = tclamp(f[s] - quot(res[s], Aii[s], rA[s]), -fl[s], fl[s]);
         de[s] = fn[s] - f[s];
         nz[s] = val[s] && lane + 32 * s >= start && de[s] != 0;
       };
@@ -875,19 +880,22 @@ template <class CX> PHASE_FN void noslip(CX& c) {
       T jn0, jn1, yn0, yn1;
       load_vec(Jn, nv, lane, jn0, jn1);
       load_vec(YT, nv, lane, yn0, yn1);
+      T k1n = K1[0], rkn = rcp_t(k1n > tiny<T>() ? k1n : tiny<T>());
       _Pragma("unroll 1") for (int t = 0; t < ntan; t++) {
-        const T j0 = jn0, j1 = jn1, y0 = yn0, y1 = yn1;
+        const T j0 = jn0, j1 = jn1, y0 = yn0, y1 = yn1, k1 = k1n, rk = rkn;
         const int row = trow[t], ci = row >> 2, k = (row & 3) - 1;
         if (t + 1 < ntan) {
           load_vec(JR + trow[t + 1] * NVP, nv, lane, jn0, jn1);
           load_vec(YT + (t + 1) * NVP, nv, lane, yn0, yn1);
+          k1n = K1[t + 1];
+          rkn = rcp_t(k1n > tiny<T>() ? k1n : tiny<T>());     // the reciprocal is ready before the dependent chain needs it
         }
         T s = j0 * (u0 + q0);
         if (nv > 32) s += j1 * (u1 + q1);
         s = warp_sum(s);
-        T mu = cmu[3 * ci + k], g = 2 * mu * s - 2 * cbt[3 * ci + k], k1 = K1[t];
+        T mu = cmu[3 * ci + k], g = 2 * mu * s - 2 * cbt[3 * ci + k];
         T f0 = ef[6 * ci + 2 * k], f1 = ef[6 * ci + 2 * k + 1], mid = T(0.5) * (f0 + f1), yold = T(0.5) * (f0 - f1), y = yold;
-        if (k1 >= T(1e-15)) y = tclamp(yold - g / k1, -mid, mid);
+        if (k1 >= T(1e-15)) y = tclamp(yold - quot(g, k1, rk), -mid, mid);
         else y = 0;
         T dy = y - yold;
         __syncwarp();
