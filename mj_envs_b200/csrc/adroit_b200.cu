@@ -69,7 +69,7 @@ template <int MC> struct MapSolveT {
                                  VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_QFC, R_ZERO | R_OUT), VR(V_DINV, R_ZERO),
                                  Reg{O_M, NTRI, R_IN},   // (A/B: reading M from L1/L2 instead costs 30 %)
                                  Reg{O_H, NTRI, 0},
-                                 Reg{O_SD, MAXSIMPLE, R_OUT}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
+                                 Reg{O_SD, MAXSIMPLE, 0}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
                                  Reg{O_AC, MC * 4, 0}, Reg{O_AV, MC * 4, 0}, Reg{O_CD, MC, 0}, Reg{O_CMU, MC * 3, R_IN},
                                  Reg{O_CAREFN, MC, 0}, Reg{O_CBT, MC * 3, R_OUT}, Reg{O_EF, MC * 6, R_OUT}, Reg{O_W, MC * 7, 0}};
   static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MC, R_IN}, Reg{I_CB1, MC, R_IN}, Reg{I_CB2, MC, R_IN},

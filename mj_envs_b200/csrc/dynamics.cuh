@@ -705,13 +705,16 @@ template <typename T> PHASE_FN void ltdl_factor(const DModel<T>& m, T* A, T* din
   const int n = m.nv;
   // schedule words (host-built): packed offset of A[i][j] | i << 10 | j << 16.  The first pass of the NEXT pivot's
   // words is fetched while the current pivot is eliminated: no model-table load on the chain of the 33 serial pivots.
-  int beg = m.ld_start[n - 1], end = m.ld_start[n];
+  // (the pivot start offsets sit in two registers per lane, so the prefetch address is one shuffle away)
+  const int ls0 = lane <= n ? m.ld_start[lane] : 0, ls1 = lane + 32 <= n ? m.ld_start[lane + 32] : 0;
+  auto start = [&](int k) { return k < 32 ? __shfl_sync(0xffffffffu, ls0, k) : __shfl_sync(0xffffffffu, ls1, k - 32); };
+  int beg = start(n - 1), end = start(n);
   int nxt = beg + lane < end ? m.ld_pair[beg + lane] : 0;
   for (int k = n - 1; k >= 0; k--) {
     const int cb = beg, ce = end, cur = nxt;
     if (k > 0) {
       end = beg;
-      beg = m.ld_start[k - 1];
+      beg = start(k - 1);
       nxt = beg + lane < end ? m.ld_pair[beg + lane] : 0;
     }
     const T* rk = A + rowoff(k);
