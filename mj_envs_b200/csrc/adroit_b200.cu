@@ -50,9 +50,11 @@ struct MapSmooth {
                                  Reg{O_CRB, NBP * 10, 0}, Reg{O_M, NTRI, R_OUT}, Reg{O_H, NTRI, 0}};
   static constexpr Reg RI[NI] = {Reg{I_SURV, 4, 0}};
 };
+// the geom frames (written by the smooth kernel) are staged: the broad phase walks ~250 candidate pairs per env and
+// every test starts with two position reads; the kernel is register-bound (2 blocks/SM), shared memory is free
 struct MapCollide {
-  static constexpr int NT = 1, NI = 1;
-  static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}};
+  static constexpr int NT = 3, NI = 1;
+  static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}, Reg{SM_T + G_GPOS, NGP * 3, R_IN}, Reg{SM_T + G_GMAT, NGP * 9, R_IN}};
   static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV, 0}};
 };
 // The solve kernel comes in two size classes (MC = contact capacity of the shared-memory tables): envs with at most
