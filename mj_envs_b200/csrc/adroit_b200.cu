@@ -697,9 +697,25 @@ int run_range(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, 
 // then fills the SMs that the last, partly empty wave of another sub-batch's kernel leaves idle, and kernels bound by
 // different resources (registers: collide, shared memory: solve) share an SM.  Per-phase profiling and debug exports
 // use one range on the caller's stream.
+// Host buffers of adroit_step_host: every sub-batch copies ITS slice of the action in at the head of its chain and its
+// slices of the results out at the tail, on its own stream -- the copies of one sub-batch overlap the kernels of the others.
+struct HostIO { const float* action; float* obs; float* reward; uint8_t* done; uint8_t* goal; };
+static int host_in(adroit_sim* s, const HostIO* h, float* action_dev, int e0, int e1, cudaStream_t st) {
+  if (h && h->action) CK(cudaMemcpyAsync(action_dev + (size_t)e0 * s->nu, h->action + (size_t)e0 * s->nu, (size_t)(e1 - e0) * s->nu * sizeof(float), cudaMemcpyHostToDevice, st));
+  return 0;
+}
+static int host_out(adroit_sim* s, const HostIO* h, const float* obs, const float* reward, const uint8_t* done, const uint8_t* goal, int e0, int e1, cudaStream_t st) {
+  if (!h) return 0;
+  const size_t n = (size_t)(e1 - e0);
+  if (h->obs) CK(cudaMemcpyAsync(h->obs + (size_t)e0 * s->obs_dim, obs + (size_t)e0 * s->obs_dim, n * s->obs_dim * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (h->reward) CK(cudaMemcpyAsync(h->reward + e0, reward + e0, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (h->done) CK(cudaMemcpyAsync(h->done + e0, done + e0, n, cudaMemcpyDeviceToHost, st));
+  if (h->goal) CK(cudaMemcpyAsync(h->goal + e0, goal + e0, n, cudaMemcpyDeviceToHost, st));
+  return 0;
+}
 template <typename T>
 int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, const float* action, const uint8_t* mask, float* obs, float* reward,
-          uint8_t* done, uint8_t* goal, int debug, cudaStream_t stream) {
+          uint8_t* done, uint8_t* goal, int debug, cudaStream_t stream, const HostIO* hio = nullptr) {
   PArgs a;
   memset(&a, 0, sizeof a);
   a.debug = debug;
@@ -709,7 +725,9 @@ int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, cons
   nsub = (st.n + per - 1) / per;
   if (nsub <= 1) {
     a.env0 = 0; a.env1 = st.n;
-    return run_range(s, m, st, mode, a, action, mask, obs, reward, done, goal, stream);
+    if (host_in(s, hio, const_cast<float*>(action), 0, st.n, stream)) return 1;
+    if (run_range(s, m, st, mode, a, action, mask, obs, reward, done, goal, stream)) return 1;
+    return host_out(s, hio, obs, reward, done, goal, 0, st.n, stream);
   }
   CK(cudaEventRecord(s->fork_ev, stream));
   for (int c = 0; c < nsub; c++) {
@@ -717,7 +735,9 @@ int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, cons
     CK(cudaStreamWaitEvent(ss, s->fork_ev, 0));
     a.env0 = c * per;
     a.env1 = (c + 1) * per < st.n ? (c + 1) * per : st.n;
+    if (host_in(s, hio, const_cast<float*>(action), a.env0, a.env1, ss)) return 1;
     if (run_range(s, m, st, mode, a, action, mask, obs, reward, done, goal, ss)) return 1;
+    if (host_out(s, hio, obs, reward, done, goal, a.env0, a.env1, ss)) return 1;
     CK(cudaEventRecord(s->sub_done[c], ss));
     CK(cudaStreamWaitEvent(stream, s->sub_done[c], 0));
   }
@@ -733,10 +753,10 @@ int ensure_stage(adroit_sim* s, size_t n) {
 }
 
 int run(adroit_sim* s, int mode, const float* action, const uint8_t* mask, float* obs, float* reward, uint8_t* done, uint8_t* goal,
-        int debug, void* stream) {
+        int debug, void* stream, const HostIO* hio = nullptr) {
   CK(cudaSetDevice(s->device));
-  if (s->f64) return run_t<double>(s, s->md, s->sd, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
-  return run_t<float>(s, s->mf, s->sf, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream);
+  if (s->f64) return run_t<double>(s, s->md, s->sd, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream, hio);
+  return run_t<float>(s, s->mf, s->sf, mode, action, mask, obs, reward, done, goal, debug, (cudaStream_t)stream, hio);
 }
 
 // host fp64 [n][w]  ->  device typed [n][stride]
@@ -880,12 +900,8 @@ int adroit_step_host(adroit_sim* s, const float* action_host, float* obs_host, f
     CK(cudaMalloc((void**)&s->d_done, n));
     CK(cudaMalloc((void**)&s->d_goal, n));
   }
-  CK(cudaMemcpyAsync(s->d_action, action_host, n * s->nu * sizeof(float), cudaMemcpyHostToDevice, st));
-  if (run(s, MODE_STEP, s->d_action, nullptr, s->d_obs, s->d_reward, s->d_done, s->d_goal, 0, stream)) return 1;
-  if (obs_host) CK(cudaMemcpyAsync(obs_host, s->d_obs, n * s->obs_dim * sizeof(float), cudaMemcpyDeviceToHost, st));
-  if (reward_host) CK(cudaMemcpyAsync(reward_host, s->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
-  if (done_host) CK(cudaMemcpyAsync(done_host, s->d_done, n, cudaMemcpyDeviceToHost, st));
-  if (goal_host) CK(cudaMemcpyAsync(goal_host, s->d_goal, n, cudaMemcpyDeviceToHost, st));
+  const HostIO hio = {action_host, obs_host, reward_host, done_host, goal_host};   // copies are issued per sub-batch (run_t)
+  if (run(s, MODE_STEP, s->d_action, nullptr, s->d_obs, s->d_reward, s->d_done, s->d_goal, 0, stream, &hio)) return 1;
   CK(cudaStreamSynchronize(st));
   return 0;
 }
