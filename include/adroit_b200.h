@@ -60,7 +60,8 @@ int adroit_step(adroit_sim* sim, const float* action_dev, float* obs_dev, float*
                 uint8_t* done_dev, uint8_t* goal_dev, void* stream);
 
 /* Host-buffer convenience used by the reference-facing plugin: copies the action H2D, steps, copies the
- * four results D2H on `stream` and synchronises it.  Host pointers should be pinned for full speed. */
+ * four results D2H and synchronises `stream` (the copies are issued per sub-batch of envs, each on the stream
+ * of its kernels, so they overlap the other sub-batches' compute).  Host pointers should be pinned for full speed. */
 int adroit_step_host(adroit_sim* sim, const float* action_host, float* obs_host, float* reward_host,
                      uint8_t* done_host, uint8_t* goal_host, void* stream);
 
