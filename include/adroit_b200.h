@@ -65,8 +65,16 @@ int adroit_step(adroit_sim* sim, const float* action_dev, float* obs_dev, float*
 int adroit_step_host(adroit_sim* sim, const float* action_host, float* obs_host, float* reward_host,
                      uint8_t* done_host, uint8_t* goal_host, void* stream);
 
-/* sim.forward() + get_obs() (hammer_v0.py:92-104,131; door_v0.py:87-101; pen_v0.py:104-113; relocate_v0.py:74-83). */
+/* get_obs() (hammer_v0.py:92-104, door_v0.py:87-101, pen_v0.py:104-113, relocate_v0.py:74-83): packs the observation
+ * from qpos / qvel and the task frames cached by the LAST forward.  Runs no forward itself -- like the reference, whose
+ * get_obs reads data.site_xpos as mj_step / sim.forward() left it; call adroit_forward first where the reference does
+ * (hammer_v0.py:131). */
 int adroit_get_obs(adroit_sim* sim, float* obs_dev, void* stream);
+
+/* sim.forward() = mj_forward on the current state of every env (hammer_v0.py:131,152; door_v0.py:110,138;
+ * pen_v0.py:123,152; relocate_v0.py:94,129): refreshes frames, contacts, constraint forces and the cached task frames.
+ * Enqueued on `stream`, no synchronisation. */
+int adroit_forward(adroit_sim* sim, void* stream);
 
 /* get_env_state / set_env_state payload (hammer_v0.py:134-153, door_v0.py:121-138, pen_v0.py:134-152,
  * relocate_v0.py:105-129): qpos [n,nq], qvel [n,nv], par [n,npar] (the per-env model fields reset_model
@@ -76,17 +84,22 @@ int adroit_get_obs(adroit_sim* sim, float* obs_dev, void* stream);
 int adroit_get_state(adroit_sim* sim, double* qpos_host, double* qvel_host, double* par_host, void* stream);
 int adroit_set_state(adroit_sim* sim, const double* qpos_host, const double* qvel_host, const double* par_host,
                      void* stream);
+/* Episode step counter of every env (gym's TimeLimit._elapsed_steps, max_episode_steps of mj_envs_vision/__init__.py:4-29):
+ * t [n] i32, host.  With ADROIT_AUTO_RESET an env resets when its counter reaches the horizon, so staggered counters
+ * spread the resets of a batch over the episode (bench.py de-phases its batches with it).  Synchronises. */
+int adroit_set_elapsed_steps(adroit_sim* sim, const int32_t* t_host, void* stream);
 /* qacc_warmstart import/export [n,nv] (parity tests start both implementations from identical solver state). */
 int adroit_get_warmstart(adroit_sim* sim, double* w_host, void* stream);
 int adroit_set_warmstart(adroit_sim* sim, const double* w_host, void* stream);
 
-/* data.body_xpos / body_xquat / site_xpos after the last forward (debug + parity; fp64 host buffers
- * [n,nbody,3], [n,nbody,4], [n,nsite,3]; NULL to skip).  Synchronises. */
+/* data.body_xpos / body_xquat / site_xpos as the last forward left them (hammer_v0.py:141, relocate_v0.py:112-114 read
+ * them in get_env_state WITHOUT a forward: after a step they lag qpos by one substep); fp64 host buffers
+ * [n,nbody,3], [n,nbody,4], [n,nsite,3]; NULL to skip.  A pure read: no forward, no side effect.  Synchronises. */
 int adroit_get_frames(adroit_sim* sim, double* body_xpos_host, double* body_xquat_host, double* site_xpos_host,
                       void* stream);
 
-/* Solver introspection after the last substep, fp64 host buffers (NULL to skip):
- * qacc [n,nv], ncon [n] (i32), nefc [n] (i32), sensordata S_nail [n].  Synchronises. */
+/* Solver introspection, fp64 host buffers (NULL to skip): data.qacc [n,nv], ncon [n] (i32), nefc [n] (i32) and
+ * sensordata[S_nail] [n] (hammer_v0.py:102) as the last forward left them.  A pure read.  Synchronises. */
 int adroit_get_solver(adroit_sim* sim, double* qacc_host, int32_t* ncon_host, int32_t* nefc_host,
                       double* touch_host, void* stream);
 

@@ -15,8 +15,10 @@ SYMBOLS = {
     "step": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "step_host": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "get_obs": (C.c_int, [_VP, _VP, _VP]),
+    "forward": (C.c_int, [_VP, _VP]),
     "get_state": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "set_state": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    "set_elapsed_steps": (C.c_int, [_VP, _VP, _VP]),
     "get_warmstart": (C.c_int, [_VP, _VP, _VP]),
     "set_warmstart": (C.c_int, [_VP, _VP, _VP]),
     "get_frames": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),

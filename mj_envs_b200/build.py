@@ -5,7 +5,9 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "adroit_b200.cu")
 LIB = os.path.join(HERE, "libadroit_b200.so")
-DEPS = [os.path.join(HERE, "csrc", f) for f in ("adroit_b200.cu", "geom.cuh", "model.cuh", "dynamics.cuh", "constraint.cuh", "task.cuh")]
+import glob
+
+DEPS = sorted(glob.glob(os.path.join(HERE, "csrc", "*.cu")) + glob.glob(os.path.join(HERE, "csrc", "*.cuh")))   # every source the library includes
 DEPS.append(os.path.join(HERE, "..", "include", "adroit_b200.h"))
 
 
@@ -19,6 +21,8 @@ def nvcc():
 def build(force=False, verbose=False, defines=(), out=None):
     """`defines`/`out` build an experiment variant (tools/ab.sh); the product library takes neither."""
     if out or defines:
+        if not out:
+            raise ValueError("an experiment variant (defines=...) needs its own output path (out=...)")
         cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--expt-relaxed-constexpr", "-shared",
                "-Xcompiler", "-fPIC", "-o", out, SRC] + [f"-D{d}" for d in defines]
         subprocess.check_call(cmd)

@@ -357,8 +357,24 @@ static thread_local char g_err[512];
 
 namespace {
 
+// model blob reader (mjcf.py::Model.to_blob).  Every table entry is checked against the blob length: a truncated or
+// corrupt file yields an error from adroit_create, never an out-of-bounds read.
 struct Blob {
   const unsigned char* b;
+  size_t len;
+  void validate() const {
+    uint64_t nf;
+    memcpy(&nf, b + 8, 8);
+    if (nf > (len - 16) / 48) throw std::string("model blob: field table exceeds the blob");
+    for (uint64_t i = 0; i < nf; i++) {
+      const unsigned char* e = b + 16 + 48 * i;
+      uint32_t dt, cnt;
+      uint64_t off;
+      memcpy(&dt, e + 32, 4); memcpy(&cnt, e + 36, 4); memcpy(&off, e + 40, 8);
+      const uint64_t w = dt == 0 ? 4 : 8;
+      if (dt > 1 || off > len || (uint64_t)cnt * w > len - off || !memchr(e, 0, 32)) throw std::string("model blob: corrupt field entry");
+    }
+  }
   const void* find(const char* name, int want_dt, int* count) const {
     uint64_t nf;
     memcpy(&nf, b + 8, 8);
@@ -375,16 +391,18 @@ struct Blob {
     }
     return nullptr;
   }
-  std::vector<int> ints(const char* n) const {
+  std::vector<int> ints(const char* n, size_t min_len = 0) const {
     int c = 0;
     const int* p = (const int*)find(n, 0, &c);
     if (!p) throw std::string("model blob misses int field ") + n;
+    if ((size_t)c < min_len) throw std::string("model blob: field too short: ") + n;
     return std::vector<int>(p, p + c);
   }
-  std::vector<double> reals(const char* n) const {
+  std::vector<double> reals(const char* n, size_t min_len = 0) const {
     int c = 0;
     const double* p = (const double*)find(n, 1, &c);
     if (!p) throw std::string("model blob misses real field ") + n;
+    if ((size_t)c < min_len) throw std::string("model blob: field too short: ") + n;
     return std::vector<double>(p, p + c);
   }
 };
@@ -441,7 +459,7 @@ struct adroit_sim {
 namespace {
 
 template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
-  auto sizes = B.ints("sizes");
+  auto sizes = B.ints("sizes", 12);
   m.nv = sizes[0]; m.nbody = sizes[1]; m.ngeom = sizes[2]; m.nsite = sizes[3]; m.nu = sizes[4]; m.ntendon = sizes[5];
   m.npair = sizes[6]; m.npar = sizes[7]; m.obs_dim = sizes[8]; m.frame_skip = sizes[9]; m.task = sizes[10]; m.horizon = sizes[11];
   if (m.nv > 36 || m.nbody > NBP || m.ngeom > NGP || m.nsite > NSP || m.npar > NPARP || m.nu > NVP)
@@ -556,7 +574,7 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
     if (m.nrender > MAXRG) throw std::string("scene has more render primitives than render.cuh's MAXRG");
     PI(m.render_int, ri);
     PR(m.render_real, B.reals("render_real"));
-    auto rc = B.reals("render_cam");
+    auto rc = B.reals("render_cam", 8);
     for (int i = 0; i < 8; i++) m.render_cam[i] = (T)rc[i];
     auto lp = B.reals("light_pos"), ld = B.reals("light_diffuse");
     auto lb = B.ints("light_body");
@@ -567,21 +585,21 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
   // stash offsets; pointers are patched once the arena is on the device
   for (auto& f : fix) *f.slot = (const void*)f.off;
 
-  auto ti = B.ints("task_int");
+  auto ti = B.ints("task_int", 16);
   for (int i = 0; i < 16; i++) m.task_int[i] = ti[i];
   auto par0 = B.reals("par0");
   for (int i = 0; i < NPARP; i++) m.par0[i] = i < (int)par0.size() ? (T)par0[i] : T(0);
-  m.touch_site = B.ints("touch_site")[0];
+  m.touch_site = B.ints("touch_site", 1)[0];
   auto ssz = B.reals("site_size");
   for (int i = 0; i < 3; i++) m.touch_size[i] = m.touch_site >= 0 ? (T)ssz[3 * m.touch_site + i] : T(0);
-  auto o = B.reals("opt_real");
-  auto oi = B.ints("opt_int");
+  auto o = B.reals("opt_real", 15);
+  auto oi = B.ints("opt_int", 3);
   m.timestep = (T)o[0]; m.gravity[0] = (T)o[1]; m.gravity[1] = (T)o[2]; m.gravity[2] = (T)o[3];
   m.tolerance = (T)o[4]; m.noslip_tolerance = (T)o[5]; m.impratio = (T)o[6]; m.solref[0] = (T)o[7]; m.solref[1] = (T)o[8];
   for (int i = 0; i < 5; i++) m.solimp[i] = (T)o[9 + i];
   m.mpr_tolerance = (T)o[14];
   m.iterations = oi[0]; m.noslip_iterations = oi[1]; m.mpr_iterations = oi[2];
-  m.meaninertia = (T)B.reals("meaninertia")[0];
+  m.meaninertia = (T)B.reals("meaninertia", 1)[0];
   m.pen_len = m.tar_len = T(1);
   if (m.task == T_PEN) {  // pen_v0.py:57-58: |object_top - object_bottom| (both sites sit on one body)
     auto sp = B.reals("site_pos");
@@ -803,28 +821,31 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
   CK(cudaSetDevice(device_id));
   adroit_sim* s = new adroit_sim();
   s->n = n_envs; s->device = device_id; s->flags = flags; s->f64 = (flags & ADROIT_F64) != 0;
-  Blob B{(const unsigned char*)model_blob};
+  Blob B{(const unsigned char*)model_blob, blob_len};
   try {
+    B.validate();
     if (s->f64) fill_model(s->md, s->arena, B); else fill_model(s->mf, s->arena, B);
   } catch (const std::string& e) {
-    delete s;
+    adroit_destroy(s);
     FAIL("%s", e.c_str());
   }
-  if (cudaMalloc((void**)&s->arena.dev, s->arena.host.size()) != cudaSuccess) { delete s; FAIL("cudaMalloc(model) failed"); }
+  // every failure below releases the handle and what it already owns (adroit_destroy), then reports
+#define CKD(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { adroit_destroy(s); FAIL("%s failed: %s", #call, cudaGetErrorString(e_)); } } while (0)
+  CKD(cudaMalloc((void**)&s->arena.dev, s->arena.host.size()));
   s->allocs.push_back(s->arena.dev);
-  CK(cudaMemcpy(s->arena.dev, s->arena.host.data(), s->arena.host.size(), cudaMemcpyHostToDevice));
-  if (s->f64 ? configure_kernels<double>() : configure_kernels<float>()) { delete s; return 1; }
+  CKD(cudaMemcpy(s->arena.dev, s->arena.host.data(), s->arena.host.size(), cudaMemcpyHostToDevice));
+  if (s->f64 ? configure_kernels<double>() : configure_kernels<float>()) { adroit_destroy(s); return 1; }
   {
     const char* e = getenv("ADROIT_SUBBATCHES");
     // default: sub-batches of >= 2048 envs, at most ADROIT_DEFAULT_SUBBATCHES of them (measured: profiles/r3_subbatches.txt)
     int want = e ? atoi(e) : (n_envs / 2048 < ADROIT_DEFAULT_SUBBATCHES ? n_envs / 2048 : ADROIT_DEFAULT_SUBBATCHES);
     s->nsub = want < 1 ? 1 : (want > 16 ? 16 : want);
-    CK(cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
+    CKD(cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
     for (int c = 0; c < s->nsub; c++) {
       cudaStream_t ss;
       cudaEvent_t ev;
-      CK(cudaStreamCreateWithFlags(&ss, cudaStreamNonBlocking));
-      CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+      CKD(cudaStreamCreateWithFlags(&ss, cudaStreamNonBlocking));
+      CKD(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
       s->sub_stream.push_back(ss);
       s->sub_done.push_back(ev);
     }
@@ -853,6 +874,7 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
   s->allocs.push_back(s->d_out4);
   if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr)) { adroit_destroy(s); return 1; }
   if (cudaDeviceSynchronize() != cudaSuccess) { adroit_destroy(s); FAIL("initial forward failed: %s", cudaGetErrorString(cudaGetLastError())); }
+#undef CKD
   *out = s;
   return 0;
 }
@@ -936,6 +958,15 @@ int adroit_set_state(adroit_sim* s, const double* qpos, const double* qvel, cons
   return 0;
 }
 
+int adroit_set_elapsed_steps(adroit_sim* s, const int32_t* t_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  if (!t_host) FAIL("t is NULL");
+  CK(cudaMemcpyAsync(s->f64 ? s->sd.t : s->sf.t, t_host, sizeof(int) * (size_t)s->n, cudaMemcpyHostToDevice, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
 int adroit_get_warmstart(adroit_sim* s, double* w, void* stream) {
   CK(cudaSetDevice(s->device));
   return download_field(s, w, CTXP, s->nv, CTX_T, V_WARM * NVP, (cudaStream_t)stream);
@@ -945,11 +976,15 @@ int adroit_set_warmstart(adroit_sim* s, const double* w, void* stream) {
   return upload_field(s, w, CTXP, s->nv, CTX_T, V_WARM * NVP, (cudaStream_t)stream);
 }
 
+int adroit_forward(adroit_sim* s, void* stream) {
+  return run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, stream);
+}
+
 int adroit_get_frames(adroit_sim* s, double* bx, double* bq, double* sx, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   CK(cudaSetDevice(s->device));
-  // frames are exported by a debug forward on the current state
-  if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
+  // a pure read of the context block: the frames of the LAST forward (one substep behind qpos after a step, exactly
+  // what mujoco-py's data.body_xpos / site_xpos hold when the reference's get_env_state reads them, hammer_v0.py:134-142)
   if (bx && download_field(s, bx, CTXP, 3 * s->nbody, CTX_T, O_XPOS, st)) return 1;
   if (bq && download_field(s, bq, CTXP, 4 * s->nbody, CTX_T, O_XQUAT, st)) return 1;
   if (sx && download_field(s, sx, CTXP, 3 * s->nsite, CTX_T, SM_T + G_SPOS, st)) return 1;
@@ -959,7 +994,7 @@ int adroit_get_frames(adroit_sim* s, double* bx, double* bq, double* sx, void* s
 int adroit_get_solver(adroit_sim* s, double* qacc, int32_t* ncon, int32_t* nefc, double* touch, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   CK(cudaSetDevice(s->device));
-  if (run(s, MODE_FORWARD, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, stream)) return 1;
+  // a pure read, like adroit_get_frames: qacc, the contact / row counts and the touch reading of the LAST forward
   if (qacc && download_field(s, qacc, CTXP, s->nv, CTX_T, V_QACC * NVP, st)) return 1;
   if (touch && download_field(s, touch, CTXP, 1, CTX_T, O_TF + 19, st)) return 1;
   if (ncon || nefc) {

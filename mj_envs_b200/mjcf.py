@@ -438,6 +438,13 @@ def load_mjcf(path: str, task: str | None = None) -> Model:
             for ch in sec:
                 sensors.append(dict(type=ch.tag, name=ch.attrib.get("name", ""), site=ch.attrib.get("site")))
 
+    # MuJoCo numbers the elements body by body (mjCModel::MakeLists: a body's own joints / geoms / sites / cameras /
+    # lights, then its children), not in document order: an element declared AFTER a child body (the world's
+    # `uprightwall` geom, relocate's `target` and pen's `eps_ball` sites) still precedes every element of that child.
+    # Ids are visible to the reference through placeholder ids (relocate's first reset_model writes
+    # site_pos[0], which is `target` only under this numbering), so reproduce it.
+    for lst in (joints, geoms, sites, cams, lights):
+        lst.sort(key=lambda e: e["body"])          # stable: document order within a body
     return _compile(task, opt, bodies, joints, geoms, sites, cams, lights, pairs_x, excludes, tendons,
                     actuators, sensors)
 

@@ -59,15 +59,37 @@ class Box:
         return rng.uniform(-1, 1, self.shape).astype(self.dtype)
 
 
+def evaluate_success(env_id: str, paths) -> float:
+    """hammer_v0.py:167-175 / door_v0.py:149-157 / relocate_v0.py:141-149 (> 25 goal steps); pen_v0.py:180-188 (> 20)."""
+    thr = 20 if env_id == "pen-v0" else 25
+    num_success = sum(1 for path in paths if np.sum(np.asarray(path["env_infos"]["goal_achieved"])) > thr)
+    return num_success * 100.0 / len(paths)
+
+
 class AdroitVecEnv:
-    def __init__(self, env_id: str, num_envs: int, device: int | str | torch.device = 0, seed: int = 0,
+    """`render_mode, width, height, is_headless, variation_type` are the reference constructors' arguments
+    (hammer_v0.py:12, door_v0.py:15, pen_v0.py:12, relocate_v0.py:11; passed by helpers.py:59-63 through gym.make):
+    accepted with the same names and defaults.  `render_mode` / `is_headless` choose between a GL window and the EGL
+    offscreen observer there; here every pixel comes from the CUDA ray-caster (`render()`), so they are stored, not acted
+    on.  `width` / `height` must be 64: the only size the reference's make_env passes and the one the kernel is built for.
+    `strict_capacity=True` makes `step` raise when a per-env contact / constraint-row buffer overflowed (the dropped
+    entries are otherwise only counted, see `overflow()`; capacity = the reference model's nconmax=100, DAPG_assets.xml:4)."""
+
+    def __init__(self, env_id: str, num_envs: int = 1, device: int | str | torch.device = 0, seed: int = 0,
                  variation_type=None, fp64: bool = False, auto_reset: bool = False, reset_on_done: bool = False,
-                 env_id_offset: int = 0, frame_skip: int | None = None, model: Model | None = None):
+                 env_id_offset: int = 0, frame_skip: int | None = None, model: Model | None = None,
+                 render_mode=None, width: int = 64, height: int = 64, is_headless: bool = False, strict_capacity: bool = False):
         if env_id not in ENV_IDS:
             raise ValueError(f"unknown env id {env_id!r}; expected one of {sorted(ENV_IDS)}")
+        if render_mode not in (None, "rgb_array", "human"):
+            raise ValueError(f"unsupported render_mode {render_mode!r}")
+        if (width, height) != (64, 64):
+            raise ValueError("the pixel path renders 64x64 (helpers.py:63); other sizes are not built")
         if not torch.cuda.is_available():
             raise RuntimeError("AdroitVecEnv needs a CUDA device (no CPU fallback)")
         self.env_id = env_id
+        self.render_mode, self.width, self.height, self.is_headless = render_mode, width, height, is_headless
+        self.strict_capacity = strict_capacity
         self.device = torch.device(device if not isinstance(device, int) else f"cuda:{device}")
         self.num_envs = int(num_envs)
         self.model = model if model is not None else load_compiled(ENV_IDS[env_id])
@@ -76,7 +98,8 @@ class AdroitVecEnv:
         self.variation_type = variation_type
         if variation_type is not None and env_id == "hammer-v0":
             self.model = self.model.with_variation(variation_type)
-        if frame_skip is not None:
+        if frame_skip is not None:        # a private copy: a caller-supplied `model` is never edited in place
+            self.model = Model(task=self.model.task, names=self.model.names, A=dict(self.model.A))
             self.model.A["sizes"] = self.model.A["sizes"].copy()
             self.model.A["sizes"][9] = frame_skip
         self.abi = cuda_abi()
@@ -128,7 +151,19 @@ class AdroitVecEnv:
         a = torch.as_tensor(action, dtype=torch.float32, device=self.device).reshape(self.num_envs, self.nu).contiguous()
         self.abi.check(self.abi.step(self._h, a.data_ptr(), self._obs.data_ptr(), self._rew.data_ptr(), self._done.data_ptr(),
                                      self._goal.data_ptr(), self._stream()))
+        if self.strict_capacity:
+            self.check_capacity()
         return self._obs.clone(), self._rew.clone(), self._done.bool(), {"goal_achieved": self._goal.bool()}
+
+    def check_capacity(self):
+        """Raise if any env ever had more contacts / constraint rows than the kernels keep (results would differ from the reference's)."""
+        o = self.overflow()
+        if o.sum():
+            raise RuntimeError(f"capacity overflow: {int(o[0])} contacts and {int(o[1])} constraint rows were dropped")
+
+    def forward(self):
+        """sim.forward() (hammer_v0.py:131): mj_forward on the current state; refreshes the frames get_obs / get_env_state read."""
+        self.abi.check(self.abi.forward(self._h, self._stream()))
 
     def step_host(self, action: np.ndarray, obs: np.ndarray, reward: np.ndarray, done: np.ndarray, goal: np.ndarray):
         """Reference-facing call with HOST buffers (pinned for full speed): H2D action, step, D2H results, synchronised."""
@@ -161,47 +196,52 @@ class AdroitVecEnv:
         self.abi.check(self.abi.set_state(self._h, g(q), g(v), g(p), self._stream()))
 
     def get_env_state(self):
+        """The reference's state dicts, batched: every value a float64 tensor [N, ...] (host).  Like the reference, no
+        forward is run: `target_pos` / `obj_pos` / `palm_pos` are data.site_xpos / body_xpos as the last mj_forward left
+        them, one substep behind qpos after a step (hammer_v0.py:134-142, relocate_v0.py:105-116)."""
         q, v, p = self._raw_state()
         task = ENV_IDS[self.env_id]
+        T = lambda a: torch.from_numpy(np.ascontiguousarray(a))
         if task == "hammer":     # hammer_v0.py:134-142
             _, _, sx = self.frames()
-            return dict(qpos=q, qvel=v, board_pos=p[:, :3].copy(), target_pos=sx[:, self.model.name2id("site", "S_target")].copy())
+            return dict(qpos=T(q), qvel=T(v), board_pos=T(p[:, :3]), target_pos=T(sx[:, self.model.name2id("site", "S_target")]))
         if task == "door":       # door_v0.py:121-128
-            return dict(qpos=q, qvel=v, door_body_pos=p[:, :3].copy())
+            return dict(qpos=T(q), qvel=T(v), door_body_pos=T(p[:, :3]))
         if task == "pen":        # pen_v0.py:134-141
-            return dict(qpos=q, qvel=v, desired_orien=p[:, :4].copy())
+            return dict(qpos=T(q), qvel=T(v), desired_orien=T(p[:, :4]))
         bx, _, sx = self.frames()  # relocate_v0.py:105-116
         m = self.model
-        return dict(hand_qpos=q[:, :30].copy(), obj_pos=bx[:, m.name2id("body", "Object")].copy(),
-                    target_pos=sx[:, m.name2id("site", "target")].copy(), palm_pos=sx[:, m.name2id("site", "S_grasp")].copy(),
-                    qpos=q, qvel=v)
+        return dict(hand_qpos=T(q[:, :30]), obj_pos=T(bx[:, m.name2id("body", "Object")]),
+                    target_pos=T(sx[:, m.name2id("site", "target")]), palm_pos=T(sx[:, m.name2id("site", "S_grasp")]),
+                    qpos=T(q), qvel=T(v))
 
     def set_env_state(self, state_dict):
+        """set_state(qpos, qvel) + the model fields of the dict + sim.forward(); values may be tensors or arrays [N, ...]."""
+        A = lambda x: x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else np.asarray(x)
         task = ENV_IDS[self.env_id]
         _, _, p = self._raw_state()
         if task == "hammer":     # hammer_v0.py:144-153
-            p[:, :3] = state_dict["board_pos"]
+            p[:, :3] = A(state_dict["board_pos"])
         elif task == "door":     # door_v0.py:130-138
-            p[:, :3] = state_dict["door_body_pos"]
+            p[:, :3] = A(state_dict["door_body_pos"])
         elif task == "pen":      # pen_v0.py:143-152
-            p[:, :4] = state_dict["desired_orien"]
+            p[:, :4] = A(state_dict["desired_orien"])
         else:                    # relocate_v0.py:118-129 (writes the world-frame obj_pos into model.body_pos)
-            p[:, :3] = state_dict["obj_pos"]
-            p[:, 3:6] = state_dict["target_pos"]
-        self._set_raw_state(state_dict["qpos"], state_dict["qvel"], p)
+            p[:, :3] = A(state_dict["obj_pos"])
+            p[:, 3:6] = A(state_dict["target_pos"])
+        self._set_raw_state(A(state_dict["qpos"]), A(state_dict["qvel"]), p)
 
     # ------------------------------------------------------------------ success / statistics
     def evaluate_success(self, paths):
-        """hammer_v0.py:167-175 / door_v0.py:149-157 / relocate_v0.py:141-149 (>25 goal steps); pen_v0.py:180-188 (>20)."""
-        thr = 20 if self.env_id == "pen-v0" else 25
-        num_success = sum(1 for path in paths if np.sum(np.asarray(path["env_infos"]["goal_achieved"])) > thr)
-        return num_success * 100.0 / len(paths)
+        return evaluate_success(self.env_id, paths)
 
     def reduce_episode(self, flush_running=False, all_reduce=True):
         """[sum of episode returns, #episodes with any goal, #episodes with >thr goal steps, #episodes] over all envs
         (and over all ranks with one NCCL all-reduce when torch.distributed is initialised; eval.py:69-97 semantics)."""
         out = np.zeros(4)
         self.abi.check(self.abi.reduce_episode(self._h, int(flush_running), out.ctypes.data, self._stream()))
+        if self.strict_capacity:
+            self.check_capacity()
         if all_reduce:
             from .sharding import allreduce_stats
             out = allreduce_stats(out, self.device)
@@ -219,6 +259,11 @@ class AdroitVecEnv:
         qacc, ncon, nefc, touch = np.zeros((n, self.nv)), np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n)
         self.abi.check(self.abi.get_solver(self._h, qacc.ctypes.data, ncon.ctypes.data, nefc.ctypes.data, touch.ctypes.data, self._stream()))
         return qacc, ncon, nefc, touch
+
+    def set_elapsed_steps(self, t):
+        """Per-env episode step counters (TimeLimit._elapsed_steps); with auto_reset an env resets when its counter reaches the horizon."""
+        t = np.ascontiguousarray(np.asarray(t, dtype=np.int32).reshape(self.num_envs))
+        self.abi.check(self.abi.set_elapsed_steps(self._h, t.ctypes.data, self._stream()))
 
     def get_warmstart(self):
         w = np.zeros((self.num_envs, self.nv))
@@ -261,5 +306,7 @@ class AdroitVecEnv:
 
 
 def make(env_id: str, num_envs: int = 1, **kw) -> AdroitVecEnv:
-    """gym.make-style constructor for the registered ids (mj_envs_vision/__init__.py:4-29)."""
+    """gym.make-style constructor for the registered ids (mj_envs_vision/__init__.py:4-29); takes the reference's
+    keyword arguments, so helpers.py:59-63's call `gym.make(id, is_headless=..., variation_type=..., render_mode='rgb_array',
+    width=64, height=64)` works verbatim."""
     return AdroitVecEnv(env_id, num_envs, **kw)

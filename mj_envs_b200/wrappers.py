@@ -127,12 +127,7 @@ def step(env, action: torch.Tensor):
 
 
 # ---------------------------------------------------------------- paths (hammer_v0.py:167-175 and twins; eval.py:69-97)
-def evaluate_success(env_id: str, paths) -> float:
-    """Percentage of paths with more than 25 (pen: 20) goal_achieved steps
-    (hammer_v0.py:167-175, door_v0.py:149-157, relocate_v0.py:141-149; pen_v0.py:180-188)."""
-    thr = 20 if env_id == "pen-v0" else 25
-    num_success = sum(1 for path in paths if np.sum(np.asarray(path["env_infos"]["goal_achieved"])) > thr)
-    return num_success * 100.0 / len(paths)
+from .vec_env import evaluate_success  # noqa: E402,F401  (hammer_v0.py:167-175 and twins; one implementation, re-exported here)
 
 
 def collect_paths(env: AdroitVecEnv, policy, horizon: int | None = None, record_state: bool = False):

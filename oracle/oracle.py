@@ -91,6 +91,10 @@ class OracleSim:
         q, v, p = c(qpos, self.nv), c(qvel, self.nv), c(par, self.npar)
         self.abi.check(self.abi.set_state(self.h, _p(q), _p(v), _p(p), None))
 
+    def set_elapsed_steps(self, t):
+        t = np.ascontiguousarray(t, dtype=np.int32).reshape(self.n)
+        self.abi.check(self.abi.set_elapsed_steps(self.h, _p(t), None))
+
     def get_warmstart(self):
         w = np.zeros((self.n, self.nv))
         self.abi.check(self.abi.get_warmstart(self.h, _p(w), None))

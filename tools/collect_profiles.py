@@ -5,7 +5,7 @@ tag = sys.argv[1]
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 src, dst = os.path.join(R, "gpurun_out"), os.path.join(R, "profiles")
 lines = [f"# profiles/ — evidence of run `{tag}` (see DESIGN.md §5)\n",
-         "The tags r1 … r9 are successive evidence runs (`tools/gpu_roundN.sh`, one `gpurun` call each) inside build round 1; "
+         "Evidence runs are made by `tools/gpu_evidence.sh TAG` (one `gpurun` call each); tags r1…r9 = build round 1, R2* = build round 2. "
          f"`{tag}` is the current state of the code, the older files are kept as the history DESIGN.md §5 quotes. Each run: "
          "`pytest -m gpu`, `smoke()`, `bench.py` on the default workload (with the CPU arm) and on the other three tasks + the pixel "
          "config, the ncu launch lists (`--metrics gpu__time_duration.sum … --clock-control none`), and one `ncu --set full` capture "
