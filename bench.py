@@ -226,7 +226,7 @@ def main():
     ap.add_argument("--pixels", action="store_true", help="same as the :pixels workload option")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--no-dephase", action="store_true", help="time from the start of the episodes (all envs in phase), as round 1 did")
-    ap.add_argument("--also", default=None, help="comma list of extra workloads reported under 'also' ('' = none); default: the other BASELINE configs at N=1, "
+    ap.add_argument("--also", default=None, help="comma list of extra workloads reported under 'also' ('' or 'none' = none); default: the other BASELINE configs at N=1, "
                                                  "relocate-v0:8192 (= configs[3] at 8 GPUs) at N>1")
     ap.add_argument("--e2e-steps", type=int, default=200, help="the end-to-end legs time max(steps, this) steps")
     args = ap.parse_args()
@@ -431,6 +431,8 @@ def main():
         "overflow": r["overflow"],
     }
     also = args.also if args.also is not None else (DEFAULT_ALSO if world == 1 else "relocate-v0:8192")
+    if also in ("none", "''", '""'):
+        also = ""
     if also:
         line["also"] = {}
         for w in also.split(","):
