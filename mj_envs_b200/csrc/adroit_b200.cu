@@ -43,7 +43,7 @@ struct PArgs {
 // ---- shared-memory maps of the phase kernels (everything not listed is addressed in the context block directly)
 struct MapSmooth {
   static constexpr int NT = 17, NI = 1;
-  static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_CTRL, R_IN | R_OUT), VR(V_QFS, R_ZERO | R_OUT),
+  static constexpr Reg RT[NT] = {VR(V_CTRL, R_IN | R_OUT), VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_QFS, R_ZERO | R_OUT),
                                  VR(V_QAS, R_ZERO | R_OUT), VR(V_T1, R_ZERO), VR(V_T2, R_ZERO), VR(V_DINV, R_ZERO),
                                  Reg{O_PAR, NPARP, R_IN | R_OUT}, Reg{O_XPOS, NBP * 3, R_OUT}, Reg{O_XQUAT, NBP * 4, R_OUT},
                                  Reg{O_XMAT, NBP * 9, R_OUT}, Reg{O_XANC, NVP * 3, R_OUT}, Reg{O_XAXIS, NVP * 3, R_OUT},
@@ -67,8 +67,8 @@ struct MapCollide {
 constexpr int MAXCON_S = ADROIT_MAXCON_S;
 template <int MC> struct MapSolveT {
   static constexpr int NT = 24, NI = 5;
-  static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_MA, R_ZERO),
-                                 VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_QFC, R_ZERO | R_OUT), VR(V_DINV, R_ZERO),
+  static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_QFC, R_ZERO | R_OUT),
+                                 VR(V_MA, R_ZERO), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_DINV, R_ZERO),
                                  Reg{O_M, NTRI, R_IN},   // (A/B: reading M from L1/L2 instead costs 30 %)
                                  Reg{O_H, NTRI, 0},
                                  Reg{O_SD, MAXSIMPLE, 0}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
@@ -83,11 +83,20 @@ using MapSolveS = MapSolveT<MAXCON_S>;
 struct MapFinish {
   static constexpr int NT = 20, NI = 3;
   static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),
-                                 VR(V_QACC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_QFC, R_IN | R_OUT), VR(V_T1, R_ZERO),
+                                 VR(V_QACC, R_IN | R_OUT), VR(V_QFC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_T1, R_ZERO),
                                  VR(V_DINV, R_ZERO), Reg{SM_T + G_MINV, NTRI, R_IN}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},
                                  Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}, Reg{O_AV, CROWS, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
                                  Reg{O_CBT, MAXCON * 3, R_IN}, Reg{O_EF, MAXCON * 6, R_IN | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
   static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON, R_IN}, Reg{I_SURV, MAXSURV, 0}};
+};
+// the auto-reset of a step (reset_kernel): reset_model + the part of mj_forward the observation reads (kinematics, site frames)
+struct MapReset {
+  static constexpr int NT = 12, NI = 1;
+  static constexpr Reg RT[NT] = {VR(V_CTRL, R_ZERO | R_OUT), VR(V_QPOS, R_ZERO | R_OUT), VR(V_QVEL, R_ZERO | R_OUT), VR(V_WARM, R_ZERO | R_OUT),
+                                 Reg{O_PAR, NPARP, R_IN | R_OUT}, Reg{O_XPOS, NBP * 3, R_ZERO | R_OUT}, Reg{O_XQUAT, NBP * 4, R_ZERO | R_OUT},
+                                 Reg{O_XMAT, NBP * 9, R_ZERO | R_OUT}, Reg{O_XANC, NVP * 3, R_ZERO | R_OUT}, Reg{O_XAXIS, NVP * 3, R_ZERO | R_OUT},
+                                 Reg{SM_T + G_SPOS, NSP * 3, R_ZERO | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
+  static constexpr Reg RI[NI] = {Reg{I_SURV, 4, 0}};
 };
 #undef VR
 
@@ -113,7 +122,32 @@ template <typename T> __device__ void episode_finish(const DModel<T>& m, const D
   a[3] += 1;
 }
 
+// reset_model (hammer_v0.py:106-132, door_v0.py:103-119, pen_v0.py:115-132, relocate_v0.py:85-103): episode bookkeeping,
+// the randomised model parameters, qpos = init_qpos (zeros), qvel = 0, ctrl = 0
+template <class C, typename T> DI void reset_prologue(C& c, const DModel<T>& m, const DState<T>& st, int env) {
+  if (c.lane == 0) {
+    episode_finish(m, st, env);
+    T par[NPARP];
+    draw_params(m, st.seed, (unsigned long long)(st.env_off + env), (unsigned)st.episode[env], par);
+    T* P = c.template S<O_PAR>();
+    for (int i = 0; i < m.npar; i++) P[i] = par[i];
+    st.episode[env] += 1;
+    st.t[env] = 0;
+    st.ep_return[env] = 0;
+    st.ep_goal[env] = 0;
+  }
+  T* ctrl = c.template V<V_CTRL>();
+  _Pragma("unroll 1") for (int j = c.lane; j < NVP; j += 32) ctrl[j] = 0;
+  zero_state(c);
+}
+
 // common prologue of a phase kernel: env of this warp, context pointers, staging
+// programmatic dependent launch: the kernel may have been started while its predecessor in the stream was still draining;
+// nothing the predecessor wrote (context block, reset_flag mask, GI_NCON) is read before this point.  A no-op for launches
+// without the attribute.  The dependents are released at once: they only occupy slots that this grid no longer fills.
+#define PDL_WAIT()                                                                                                        \
+  asm volatile("griddepcontrol.wait;" ::: "memory");                                                                      \
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 #define PHASE_PROLOGUE(MAP)                                                                                             \
   extern __shared__ __align__(16) unsigned char smem_raw[];                                                              \
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;                                                            \
@@ -123,7 +157,9 @@ template <typename T> __device__ void episode_finish(const DModel<T>& m, const D
   T* sm_ = reinterpret_cast<T*>(smem_raw) + (size_t)warp * map_st<MAP>();                                                \
   int* smi_ = reinterpret_cast<int*>(smem_raw + (size_t)WPB * map_st<MAP>() * sizeof(T)) + warp * map_si<MAP>();         \
   Ctx<T, MAP> c(m, sm_, smi_, st.ctx + (size_t)env * CTX_T, st.ctxi + (size_t)env * CTX_I, lane);                        \
-  stage_in(c);                                                                                                           \
+  /* one mbarrier per warp (byte count of its bulk stage-in copies) behind the maps, inside the dynamic allocation */   \
+  unsigned long long* bar_ = reinterpret_cast<unsigned long long*>(smem_raw + (size_t)WPB * map_bytes<T, MAP>()) + 2 * warp; \
+  stage_in(c, bar_);                                                                                                     \
   __syncwarp();
 
 // ---------------------------------------------------------------- phase 1: smooth dynamics
@@ -131,25 +167,10 @@ template <typename T> __device__ void episode_finish(const DModel<T>& m, const D
 template <typename T>
 __global__ void __launch_bounds__(WPB * 32) smooth_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                            const __grid_constant__ PArgs a) {
+  PDL_WAIT()
   PHASE_PROLOGUE(MapSmooth)
   const int nv = m.nv;
-  if (a.reset) {
-    // reset_model (hammer_v0.py:106-132, door_v0.py:103-119, pen_v0.py:115-132, relocate_v0.py:85-103)
-    if (lane == 0) {
-      episode_finish(m, st, env);
-      T par[NPARP];
-      draw_params(m, st.seed, (unsigned long long)(st.env_off + env), (unsigned)st.episode[env], par);
-      T* P = c.template S<O_PAR>();
-      for (int i = 0; i < m.npar; i++) P[i] = par[i];
-      st.episode[env] += 1;
-      st.t[env] = 0;
-      st.ep_return[env] = 0;
-      st.ep_goal[env] = 0;
-    }
-    T* ctrl = c.template V<V_CTRL>();
-    _Pragma("unroll 1") for (int j = lane; j < NVP; j += 32) ctrl[j] = 0;
-    zero_state(c);
-  }
+  if (a.reset) reset_prologue(c, m, st, env);
   if (a.action) {   // action map: hammer_v0.py:55-59 (act_mid / act_rng :49-50)
     T* ctrl = c.template V<V_CTRL>();
     _Pragma("unroll 1") for (int u = lane; u < m.nu; u += 32) {
@@ -181,17 +202,41 @@ __global__ void __launch_bounds__(WPB * 32) smooth_kernel(const __grid_constant_
 template <typename T>
 __global__ void __launch_bounds__(WPB * 32) collide_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                             const __grid_constant__ PArgs a) {
+  PDL_WAIT()
   PHASE_PROLOGUE(MapCollide)
   collision(c, st.overflow);
   if (lane == 0) c.gi[GI_NCON] = c.ncon;
 }
 
+// ---------------------------------------------------------------- auto-reset inside env.step()
+// The envs the step epilogue flagged (horizon reached / reset-on-done) get reset_model and the part of the following
+// sim.forward() that get_obs() reads: kinematics and the site / body frames (hammer_v0.py:126-132: the touch sensor reads 0
+// at the reset pose, the hammer lies on the table).  One launch instead of a masked five-launch forward pass: everything
+// else a forward computes (M, contacts, qacc) is rebuilt by the first substep of the next step before anything reads it.
+template <typename T>
+__global__ void __launch_bounds__(WPB * 32) reset_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+                                                          const __grid_constant__ PArgs a) {
+  PDL_WAIT()
+  PHASE_PROLOGUE(MapReset)
+  reset_prologue(c, m, st, env);
+  kinematics(c);
+  frames_and_inertia<decltype(c), false>(c);
+  cache_task_frames(c, T(0));
+  if (a.obs) write_obs(m, c.template V<V_QPOS>(), c.template V<V_QVEL>(), c.template S<O_TF>(), a.obs + (size_t)env * m.obs_dim, lane);
+  __syncwarp();
+  stage_out(c);
+}
+
 // ---------------------------------------------------------------- phase 3: constraint rows + Newton
 // MC = MAXCON_S: envs with ncon <= MAXCON_S; MC = MAXCON: the others (see MapSolveT).  The small class is compiled for
 // 5 blocks per SM (<= 102 registers), which its shared-memory slice allows.
+#ifndef ADROIT_SOLVE_BLOCKS
+#define ADROIT_SOLVE_BLOCKS 5
+#endif
 template <typename T, int MC>
-__global__ void __launch_bounds__(WPB * 32, (MC < MAXCON && sizeof(T) == 4) ? 5 : 1)
+__global__ void __launch_bounds__(WPB * 32, (MC < MAXCON && sizeof(T) == 4) ? ADROIT_SOLVE_BLOCKS : 1)
     solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, const __grid_constant__ PArgs a) {
+  PDL_WAIT()
   if (MAXCON_S < MAXCON) {
     const int env_ = a.env0 + blockIdx.x * WPB + (threadIdx.x >> 5);
     if (env_ >= a.env1) return;
@@ -211,6 +256,7 @@ __global__ void __launch_bounds__(WPB * 32, (MC < MAXCON && sizeof(T) == 4) ? 5 
 template <typename T>
 __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                            const __grid_constant__ PArgs a) {
+  PDL_WAIT()
   PHASE_PROLOGUE(MapFinish)
   const int nv = m.nv;
   c.ncon = c.gi[GI_NCON];
@@ -447,10 +493,12 @@ struct adroit_sim {
   double* d_out4 = nullptr;
   int64_t launches = 0;
   bool profile = false;
-  std::vector<cudaEvent_t> prof_ev[4];   // event pairs per phase, pending accumulation
+  std::vector<cudaEvent_t> prof_ev[5];   // event pairs per phase (4 = reset_kernel, not reported), pending accumulation
   // sub-batch pipelining (run_t): the envs are split into nsub contiguous ranges, each advanced by its own chain of
   // phase kernels on its own stream, so that the tail of one range's kernel overlaps the other ranges' kernels
   int nsub = 1;
+  bool pdl = false;             // phase kernels chained with programmatic dependent launch (ADROIT_PDL=1)
+  bool light_reset = true;      // auto-reset of a step through reset_kernel (ADROIT_LIGHT_RESET=0: masked full forward pass)
   std::vector<cudaStream_t> sub_stream;
   std::vector<cudaEvent_t> sub_done;
   cudaEvent_t fork_ev = nullptr;
@@ -640,9 +688,12 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
   return 0;
 }
 
+// dynamic shared memory of a phase kernel: the WPB map slices + 16 bytes per warp for its stage-in mbarrier
+template <typename T, class MAP> constexpr size_t phase_smem() { return WPB * map_bytes<T, MAP>() + WPB * 16; }
+
 template <typename T, class MAP, typename K>
 int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {
-  size_t smem = WPB * map_bytes<T, MAP>();
+  size_t smem = phase_smem<T, MAP>();
   int blocks = (a.env1 - a.env0 + WPB - 1) / WPB;
   if (blocks <= 0) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -651,8 +702,19 @@ int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const D
     CK(cudaEventCreate(&e1));
     CK(cudaEventRecord(e0, stream));
   }
-  kernel<<<blocks, WPB * 32, smem, stream>>>(m, st, a);
-  CK(cudaGetLastError());
+  if (s->pdl) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(WPB * 32); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, kernel, m, st, a));
+  } else {
+    kernel<<<blocks, WPB * 32, smem, stream>>>(m, st, a);
+    CK(cudaGetLastError());
+  }
   if (s->profile) {
     CK(cudaEventRecord(e1, stream));
     s->prof_ev[phase].push_back(e0);
@@ -663,11 +725,12 @@ int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const D
 }
 
 template <typename T> int configure_kernels() {
-  CK(cudaFuncSetAttribute(smooth_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSmooth>())));
-  CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapCollide>())));
-  CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSolve>())));
-  if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapSolveS>())));
-  CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WPB * map_bytes<T, MapFinish>())));
+  CK(cudaFuncSetAttribute(smooth_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSmooth>()));
+  CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapCollide>()));
+  CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolve>()));
+  if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveS>()));
+  CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapFinish>()));
+  CK(cudaFuncSetAttribute(reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapReset>()));
   return 0;
 }
 
@@ -705,6 +768,7 @@ int run_range(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, 
   if (st.flags & ADROIT_AUTO_RESET) {
     PArgs r = a;
     r.mask = st.reset_flag; r.reset = 1; r.obs = obs; r.write_obs = obs != nullptr;
+    if (s->light_reset && !a.debug) return launch_phase<T, MapReset>(s, 4, reset_kernel<T>, m, st, r, stream);
     if (forward_pass(s, m, st, r, stream)) return 1;
   }
   return 0;
@@ -836,6 +900,10 @@ int adroit_create(const void* model_blob, size_t blob_len, int n_envs, int devic
   CKD(cudaMemcpy(s->arena.dev, s->arena.host.data(), s->arena.host.size(), cudaMemcpyHostToDevice));
   if (s->f64 ? configure_kernels<double>() : configure_kernels<float>()) { adroit_destroy(s); return 1; }
   {
+    const char* ep = getenv("ADROIT_PDL");
+    s->pdl = ep && atoi(ep) != 0;
+    const char* el = getenv("ADROIT_LIGHT_RESET");
+    s->light_reset = !el || atoi(el) != 0;
     const char* e = getenv("ADROIT_SUBBATCHES");
     // default: sub-batches of >= 2048 envs, at most ADROIT_DEFAULT_SUBBATCHES of them (measured: profiles/r3_subbatches.txt)
     int want = e ? atoi(e) : (n_envs / 2048 < ADROIT_DEFAULT_SUBBATCHES ? n_envs / 2048 : ADROIT_DEFAULT_SUBBATCHES);
@@ -1049,7 +1117,7 @@ int adroit_profile(adroit_sim* s, int enable) {
 int adroit_phase_times(adroit_sim* s, double* ms4, int64_t* n4, void* stream) {
   CK(cudaSetDevice(s->device));
   CK(cudaStreamSynchronize((cudaStream_t)stream));
-  for (int p = 0; p < 4; p++) {
+  for (int p = 0; p < 5; p++) {
     double acc = 0;
     auto& v = s->prof_ev[p];
     for (size_t i = 0; i + 1 < v.size(); i += 2) {
@@ -1059,8 +1127,8 @@ int adroit_phase_times(adroit_sim* s, double* ms4, int64_t* n4, void* stream) {
       cudaEventDestroy(v[i]);
       cudaEventDestroy(v[i + 1]);
     }
-    if (ms4) ms4[p] = acc;
-    if (n4) n4[p] = (int64_t)(v.size() / 2);
+    if (ms4 && p < 4) ms4[p] = acc;
+    if (n4 && p < 4) n4[p] = (int64_t)(v.size() / 2);
     v.clear();
   }
   return 0;
@@ -1091,7 +1159,10 @@ int adroit_debug_iscratch(adroit_sim* s, int32_t* out_host, void* stream) {
 }
 int adroit_debug_layout(int* out, int max_n) {
   const int v[] = {NVP, NBP, NGP, NSP, MAXCON, CROWS, NTRI, NPARP, NTF, G_TOTAL, GI_TOTAL, G_GPOS, G_GMAT, G_SPOS, G_CON, G_JR, G_MINV,
-                   G_DBG_M, G_DBG_BIAS, G_DBG_QFS, G_DBG_QAS, G_DBG_QACC, G_DBG_QFC, G_DBG_XPOS, G_DBG_XQUAT, G_DBG_EF, GI_CON};
+                   G_DBG_M, G_DBG_BIAS, G_DBG_QFS, G_DBG_QAS, G_DBG_QACC, G_DBG_QFC, G_DBG_XPOS, G_DBG_XQUAT, G_DBG_EF, GI_CON,
+                   // dynamic shared memory per block of the fp32 phase kernels (occupancy bookkeeping, tools/occupancy.py)
+                   (int)phase_smem<float, MapSmooth>(), (int)phase_smem<float, MapCollide>(), (int)phase_smem<float, MapSolveS>(),
+                   (int)phase_smem<float, MapSolve>(), (int)phase_smem<float, MapFinish>(), (int)phase_smem<float, MapReset>(), CTX_T, CTX_I};
   int n = (int)(sizeof v / sizeof v[0]);
   for (int i = 0; i < n && i < max_n; i++) out[i] = v[i];
   return n;

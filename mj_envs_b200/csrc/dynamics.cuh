@@ -21,6 +21,7 @@ namespace adroit {
 // resolve at compile time, so a device function works unchanged whichever side a region lives on.
 constexpr int CTX_T = SM_T + G_TOTAL;     // T words per env
 constexpr int CTX_I = SM_I + GI_TOTAL;    // int words per env
+static_assert(CTX_T % 4 == 0 && CTX_I % 4 == 0, "context blocks must stay 16-byte aligned (bulk copies)");
 enum { R_IN = 1, R_OUT = 2, R_ZERO = 4 };
 struct Reg { int off, len, flags; };
 constexpr int pad4(int x) { return (x + 3) / 4 * 4; }
@@ -73,14 +74,68 @@ template <typename T_, class MAP_> struct Ctx {
   }
 };
 
-// stage the MAP's regions between the context block and shared memory (whole warp, 16-byte chunks; region offsets and
-// lengths are multiples of 16 bytes by construction).  Loads go through cp.async so that every region is in flight at once.
+// stage the MAP's regions between the context block and shared memory.
+//
+// Blackwell-native form (ADROIT_BULK_STAGE, default): every region is ONE 1-D bulk copy issued by lane 0 --
+// `cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes` on the way in (the warp's own mbarrier counts the
+// bytes; the lanes zero the R_ZERO scratch regions meanwhile and then wait on the barrier's phase), and
+// `cp.async.bulk.global.shared::cta.bulk_group` on the way out (fire and forget: the warp only waits until the copy engine
+// has READ its shared memory, not until the data is in HBM).  Region offsets and lengths are multiples of 16 bytes by
+// construction (static_asserts below), the context blocks are 16-byte aligned (CTX_T, CTX_I multiples of 4 words).
+// Ampere-style fallback (ADROIT_BULK_STAGE=0, kept for A/B): 16-byte cp.async chunks, lanes over chunks.
+#ifndef ADROIT_BULK_STAGE
+#define ADROIT_BULK_STAGE 1
+#endif
+DI unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+DI void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");   // the copy engine (async proxy) must see the initialised barrier
+}
+DI void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+DI void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "MBAR_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra MBAR_DONE;\n"
+      "bra MBAR_WAIT;\n"
+      "MBAR_DONE:\n"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+DI void bulk_g2s(void* smem_dst, const void* gmem_src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)), "l"(gmem_src),
+               "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+DI void bulk_s2g(void* gmem_dst, const void* smem_src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
 DI void cp_async16(void* smem_dst, const void* gmem_src) {
   unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem_src) : "memory");
 }
 DI void cp_async_wait_all() { asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory"); }
-template <class CX, int I = 0> DI void stage_in_issue(CX& c) {
+template <class MAP, typename T> constexpr unsigned map_in_bytes() {
+  unsigned b = 0;
+  for (int i = 0; i < MAP::NT; i++) if (MAP::RT[i].flags & R_IN) b += MAP::RT[i].len * sizeof(T);
+  for (int i = 0; i < MAP::NI; i++) if (MAP::RI[i].flags & R_IN) b += MAP::RI[i].len * sizeof(int);
+  return b;
+}
+// Runs of regions that are adjacent in the map (hence in shared memory: lengths are multiples of 4 words) AND in the
+// context block, with the same direction flag, travel as ONE bulk copy: run_head = the run starts at region i,
+// run_len = words from region i to the end of its run.
+constexpr bool run_joins(const Reg* R, int n, int i, int flag) {   // does region i continue the run of region i-1?
+  return i > 0 && i < n && (R[i].flags & flag) && (R[i - 1].flags & flag) && R[i - 1].off + R[i - 1].len == R[i].off;
+}
+constexpr int run_len(const Reg* R, int n, int i, int flag) {
+  int len = R[i].len;
+  for (int k = i + 1; k < n && run_joins(R, n, k, flag); k++) len += R[k].len;
+  return len;
+}
+// lane 0: one bulk copy per run of R_IN regions
+template <class CX, int I = 0> DI void stage_in_bulk(CX& c, unsigned long long* bar) {
   using MAP = typename CX::MAP;
   using T = typename CX::real;
   constexpr int E = 16 / sizeof(T);
@@ -88,40 +143,103 @@ template <class CX, int I = 0> DI void stage_in_issue(CX& c) {
     constexpr Reg r = MAP::RT[I];
     constexpr int so = map_soff<MAP>(r.off);
     static_assert(r.off % E == 0 && r.len % E == 0, "regions are staged in 16-byte chunks");
-    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane * E; j < r.len; j += 32 * E) cp_async16(c.sm + so + j, c.gb + r.off + j); }
-    else if constexpr ((r.flags & R_ZERO) != 0) { for (int j = c.lane; j < r.len; j += 32) c.sm[so + j] = 0; }
-    stage_in_issue<CX, I + 1>(c);
+    if constexpr ((r.flags & R_IN) != 0 && !run_joins(MAP::RT, MAP::NT, I, R_IN))
+      bulk_g2s(c.sm + so, c.gb + r.off, run_len(MAP::RT, MAP::NT, I, R_IN) * sizeof(T), bar);
+    stage_in_bulk<CX, I + 1>(c, bar);
   } else if constexpr (I < MAP::NT + MAP::NI) {
-    constexpr Reg r = MAP::RI[I - MAP::NT];
+    constexpr int K = I - MAP::NT;
+    constexpr Reg r = MAP::RI[K];
     constexpr int so = map_ioff<MAP>(r.off);
     static_assert(r.off % 4 == 0 && r.len % 4 == 0, "regions are staged in 16-byte chunks");
-    if constexpr ((r.flags & R_IN) != 0) { for (int j = c.lane * 4; j < r.len; j += 128) cp_async16(c.smi + so + j, c.gib + r.off + j); }
-    stage_in_issue<CX, I + 1>(c);
+    if constexpr ((r.flags & R_IN) != 0 && !run_joins(MAP::RI, MAP::NI, K, R_IN))
+      bulk_g2s(c.smi + so, c.gib + r.off, run_len(MAP::RI, MAP::NI, K, R_IN) * sizeof(int), bar);
+    stage_in_bulk<CX, I + 1>(c, bar);
   }
 }
-template <class CX> DI void stage_in(CX& c) {
-  stage_in_issue(c);
-  cp_async_wait_all();
-}
-template <class CX, int I = 0> DI void stage_out(CX& c) {
+// all lanes: zero the R_ZERO regions (BULK: only those; otherwise also the cp.async chunks of the R_IN regions)
+template <class CX, bool BULK, int I = 0> DI void stage_in_issue(CX& c) {
   using MAP = typename CX::MAP;
   using T = typename CX::real;
   constexpr int E = 16 / sizeof(T);
   if constexpr (I < MAP::NT) {
     constexpr Reg r = MAP::RT[I];
     constexpr int so = map_soff<MAP>(r.off);
-    if constexpr ((r.flags & R_OUT) != 0) {
-      for (int j = c.lane * E; j < r.len; j += 32 * E) *reinterpret_cast<int4*>(c.gb + r.off + j) = *reinterpret_cast<const int4*>(c.sm + so + j);
+    static_assert(r.off % E == 0 && r.len % E == 0, "regions are staged in 16-byte chunks");
+    if constexpr ((r.flags & R_IN) != 0) { if constexpr (!BULK) for (int j = c.lane * E; j < r.len; j += 32 * E) cp_async16(c.sm + so + j, c.gb + r.off + j); }
+    else if constexpr ((r.flags & R_ZERO) != 0) { for (int j = c.lane; j < r.len; j += 32) c.sm[so + j] = 0; }
+    stage_in_issue<CX, BULK, I + 1>(c);
+  } else if constexpr (I < MAP::NT + MAP::NI) {
+    constexpr Reg r = MAP::RI[I - MAP::NT];
+    constexpr int so = map_ioff<MAP>(r.off);
+    static_assert(r.off % 4 == 0 && r.len % 4 == 0, "regions are staged in 16-byte chunks");
+    if constexpr ((r.flags & R_IN) != 0) { if constexpr (!BULK) for (int j = c.lane * 4; j < r.len; j += 128) cp_async16(c.smi + so + j, c.gib + r.off + j); }
+    stage_in_issue<CX, BULK, I + 1>(c);
+  }
+}
+// `bar`: this warp's mbarrier (8 bytes of shared memory, used for one phase)
+template <class CX> DI void stage_in(CX& c, unsigned long long* bar) {
+#if ADROIT_BULK_STAGE
+  using MAP = typename CX::MAP;
+  using T = typename CX::real;
+  constexpr unsigned bytes = map_in_bytes<MAP, T>();
+  if constexpr (bytes > 0) {
+    if (c.lane == 0) {
+      mbar_init(bar, 1);
+      mbar_expect_tx(bar, bytes);
+      stage_in_bulk(c, bar);
     }
-    stage_out<CX, I + 1>(c);
+  }
+  stage_in_issue<CX, true>(c);
+  __syncwarp();
+  if constexpr (bytes > 0) mbar_wait(bar, 0);
+#else
+  stage_in_issue<CX, false>(c);
+  cp_async_wait_all();
+#endif
+}
+template <class CX, int I = 0> DI void stage_out_regions(CX& c) {
+  using MAP = typename CX::MAP;
+  using T = typename CX::real;
+  [[maybe_unused]] constexpr int E = 16 / sizeof(T);
+  if constexpr (I < MAP::NT) {
+    constexpr Reg r = MAP::RT[I];
+    constexpr int so = map_soff<MAP>(r.off);
+    if constexpr ((r.flags & R_OUT) != 0) {
+#if ADROIT_BULK_STAGE
+      if constexpr (!run_joins(MAP::RT, MAP::NT, I, R_OUT)) bulk_s2g(c.gb + r.off, c.sm + so, run_len(MAP::RT, MAP::NT, I, R_OUT) * sizeof(T));
+#else
+      for (int j = c.lane * E; j < r.len; j += 32 * E) *reinterpret_cast<int4*>(c.gb + r.off + j) = *reinterpret_cast<const int4*>(c.sm + so + j);
+#endif
+    }
+    stage_out_regions<CX, I + 1>(c);
   } else if constexpr (I < MAP::NT + MAP::NI) {
     constexpr Reg r = MAP::RI[I - MAP::NT];
     constexpr int so = map_ioff<MAP>(r.off);
     if constexpr ((r.flags & R_OUT) != 0) {
+#if ADROIT_BULK_STAGE
+      if constexpr (!run_joins(MAP::RI, MAP::NI, I - MAP::NT, R_OUT))
+        bulk_s2g(c.gib + r.off, c.smi + so, run_len(MAP::RI, MAP::NI, I - MAP::NT, R_OUT) * sizeof(int));
+#else
       for (int j = c.lane * 4; j < r.len; j += 128) *reinterpret_cast<int4*>(c.gib + r.off + j) = *reinterpret_cast<const int4*>(c.smi + so + j);
+#endif
     }
-    stage_out<CX, I + 1>(c);
+    stage_out_regions<CX, I + 1>(c);
   }
+}
+// write the R_OUT regions back (call with the warp converged, after the last shared-memory write)
+template <class CX> DI void stage_out(CX& c) {
+#if ADROIT_BULK_STAGE
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the lanes' generic-proxy writes -> visible to the copy engine
+  __syncwarp();
+  if (c.lane == 0) {
+    stage_out_regions(c);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory may be released once it has been read
+  }
+  __syncwarp();
+#else
+  stage_out_regions(c);
+#endif
 }
 
 template <typename T> DI void quat_mul(T* r, const T* a, const T* b) {
@@ -212,7 +330,7 @@ template <class CX> PHASE_FN void kinematics(CX& c) {
 }
 
 // geom / site world frames (global scratch) and single-body inertias about the body origin
-template <class CX> PHASE_FN void frames_and_inertia(CX& c) {
+template <class CX, bool INERTIA = true> PHASE_FN void frames_and_inertia(CX& c) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
   const T *xpos = c.template S<O_XPOS>(), *xmat = c.template S<O_XMAT>(), *par = c.template S<O_PAR>();
@@ -239,7 +357,7 @@ template <class CX> PHASE_FN void frames_and_inertia(CX& c) {
   }
   // inertia {m, h[3] = m*c, I[6] = xx,yy,zz,xy,xz,yz} about xpos[b], world axes
   T* crb = c.template S<O_CRB>();
-  for (int b = c.lane; b < m.nbody; b += 32) {
+  if constexpr (INERTIA) for (int b = c.lane; b < m.nbody; b += 32) {
     T mass = (m.task_int[8] == VAR_MASS && b == m.task_int[9]) ? par[3] : m.body_mass[b], Rw[9], cv[3];   // hammer_v0.py:115-118
     const T *A = xmat + 9 * b, *B = m.body_imat + 9 * b, *dg = m.body_inertia + 3 * b;
     for (int i = 0; i < 3; i++)

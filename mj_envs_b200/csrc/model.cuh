@@ -9,14 +9,20 @@
 
 namespace adroit {
 
-constexpr int NVP = 40;        // padded dof count (Adroit scenes: 30..36)
+constexpr int NVP = 36;        // padded dof count (Adroit scenes: 30..36); a multiple of 4: vectors stay 16-byte aligned
 constexpr int NBP = 32;        // bodies (29..31)
 constexpr int NGP = 36;        // collidable geoms (26..33)
 constexpr int NSP = 32;        // sites (28..32)
 constexpr int MAXCON = 32;     // contacts kept per env (overflow is counted, see adroit_overflow)
 constexpr int CROWS = MAXCON * 4;  // contact-frame Jacobian rows: normal, 2 tangents, torsion
-constexpr int MAXSIMPLE = 96;  // friction-loss + joint-limit + tendon-limit rows
-constexpr int NTRI = 720;      // lower triangle of a 36x36 matrix, rows padded to multiples of 4 (16-byte aligned rows, see tri())
+#ifndef ADROIT_MAXSIMPLE
+#define ADROIT_MAXSIMPLE 96
+#endif
+constexpr int MAXSIMPLE = ADROIT_MAXSIMPLE;  // friction-loss + joint-limit + tendon-limit rows
+#ifndef ADROIT_NTRI
+#define ADROIT_NTRI 720
+#endif
+constexpr int NTRI = ADROIT_NTRI;      // lower triangle of a 36x36 matrix, rows padded to multiples of 4 (16-byte aligned rows, see tri())
 constexpr int NPARP = 8;       // per-env model parameters (board_pos | door_body_pos | target quat | obj pos + target pos)
 constexpr int NTF = 24;        // cached task frames (positions the observation / reward read)
 #ifndef ADROIT_WPB
@@ -34,7 +40,9 @@ enum { S_FRICTION = 0, S_JLIMIT = 1, S_TLIMIT = 2 };
 
 // ---- shared memory (per warp), offsets in units of T
 enum {
-  V_QPOS = 0, V_QVEL, V_WARM, V_CTRL, V_QFS, V_QAS, V_QACC, V_MA, V_GRAD, V_SEARCH, V_MV, V_QFC, V_T1, V_T2, V_DINV, V_COUNT
+  // persistent / handed-over vectors first, ordered so that every phase kernel's staged set is one contiguous run of the
+  // context block (smooth: CTRL..QVEL, solve: WARM..QAS in, QACC..QFC out, finish: QPOS..QFC): one bulk copy each
+  V_CTRL = 0, V_QPOS, V_QVEL, V_WARM, V_QFS, V_QAS, V_QACC, V_QFC, V_MA, V_GRAD, V_SEARCH, V_MV, V_T1, V_T2, V_DINV, V_COUNT
 };
 constexpr int O_PAR = V_COUNT * NVP;
 constexpr int O_XPOS = O_PAR + NPARP;

@@ -301,7 +301,8 @@ class AdroitVecEnv:
         n = self.abi.lib.adroit_debug_layout(v.ctypes.data, 64)
         keys = ["NVP", "NBP", "NGP", "NSP", "MAXCON", "CROWS", "NTRI", "NPARP", "NTF", "G_TOTAL", "GI_TOTAL", "G_GPOS", "G_GMAT", "G_SPOS",
                 "G_CON", "G_JR", "G_MINV", "G_DBG_M", "G_DBG_BIAS", "G_DBG_QFS", "G_DBG_QAS", "G_DBG_QACC", "G_DBG_QFC", "G_DBG_XPOS",
-                "G_DBG_XQUAT", "G_DBG_EF", "GI_CON"]
+                "G_DBG_XQUAT", "G_DBG_EF", "GI_CON", "SMEM_SMOOTH", "SMEM_COLLIDE", "SMEM_SOLVE_S", "SMEM_SOLVE", "SMEM_FINISH", "SMEM_RESET",
+                "CTX_T", "CTX_I"]
         return dict(zip(keys, map(int, v[:n])))
 
 
