@@ -42,6 +42,7 @@ struct PArgs {
 #define VR(V, F) Reg{(V) * NVP, NVP, (F)}
 // ---- shared-memory maps of the phase kernels (everything not listed is addressed in the context block directly)
 struct MapSmooth {
+  static constexpr int W = WPB;   // warps (= envs) per block of the kernel that uses this map
   static constexpr int NT = 17, NI = 1;
   static constexpr Reg RT[NT] = {VR(V_CTRL, R_IN | R_OUT), VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_QFS, R_ZERO | R_OUT),
                                  VR(V_QAS, R_ZERO | R_OUT), VR(V_T1, R_ZERO), VR(V_T2, R_ZERO), VR(V_DINV, R_ZERO),
@@ -53,6 +54,7 @@ struct MapSmooth {
 // the geom frames (written by the smooth kernel) are staged: the broad phase walks ~250 candidate pairs per env and
 // every test starts with two position reads; the kernel is register-bound (2 blocks/SM), shared memory is free
 struct MapCollide {
+  static constexpr int W = WPB;
   static constexpr int NT = 3, NI = 1;
   static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}, Reg{SM_T + G_GPOS, NGP * 3, R_IN}, Reg{SM_T + G_GMAT, NGP * 9, R_IN}};
   static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV, 0}};
@@ -65,7 +67,13 @@ struct MapCollide {
 #define ADROIT_MAXCON_S 16
 #endif
 constexpr int MAXCON_S = ADROIT_MAXCON_S;
-template <int MC> struct MapSolveT {
+#ifndef ADROIT_WPB_SOLVE
+#define ADROIT_WPB_SOLVE 5    // 4 blocks x 5 envs per SM: measured best of 4 / 5 / 10 / 20 (profiles/R2c_ab_lockstep.txt)
+#endif
+// WW = warps per block: ADROIT_WPB_SOLVE for the fp32 small class (block-lockstep Newton, constraint.cuh), WPB otherwise
+// (the big class and the fp64 build need 13-26 KB per env: more warps would not fit a block)
+template <int MC, int WW = WPB> struct MapSolveT {
+  static constexpr int W = WW;
   static constexpr int NT = 24, NI = 5;
   static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_QFC, R_ZERO | R_OUT),
                                  VR(V_MA, R_ZERO), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_DINV, R_ZERO),
@@ -77,10 +85,11 @@ template <int MC> struct MapSolveT {
   static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MC, R_IN}, Reg{I_CB1, MC, R_IN}, Reg{I_CB2, MC, R_IN},
                                  Reg{I_CMASK, MC, 0}};
 };
-using MapSolve = MapSolveT<MAXCON>;
-using MapSolveS = MapSolveT<MAXCON_S>;
+template <typename T, int MC> constexpr int solve_w() { return (sizeof(T) == 4 && MC < MAXCON) ? ADROIT_WPB_SOLVE : WPB; }
+template <typename T, int MC> using MapSolveK = MapSolveT<MC, solve_w<T, MC>()>;
 // M^-1 is staged (read-only) for the noslip sweeps; the same shared-memory region then holds the (M + hB) factor
 struct MapFinish {
+  static constexpr int W = WPB;
   static constexpr int NT = 20, NI = 3;
   static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),
                                  VR(V_QACC, R_IN | R_OUT), VR(V_QFC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_T1, R_ZERO),
@@ -91,6 +100,7 @@ struct MapFinish {
 };
 // the auto-reset of a step (reset_kernel): reset_model + the part of mj_forward the observation reads (kinematics, site frames)
 struct MapReset {
+  static constexpr int W = WPB;
   static constexpr int NT = 12, NI = 1;
   static constexpr Reg RT[NT] = {VR(V_CTRL, R_ZERO | R_OUT), VR(V_QPOS, R_ZERO | R_OUT), VR(V_QVEL, R_ZERO | R_OUT), VR(V_WARM, R_ZERO | R_OUT),
                                  Reg{O_PAR, NPARP, R_IN | R_OUT}, Reg{O_XPOS, NBP * 3, R_ZERO | R_OUT}, Reg{O_XQUAT, NBP * 4, R_ZERO | R_OUT},
@@ -151,14 +161,14 @@ template <class C, typename T> DI void reset_prologue(C& c, const DModel<T>& m, 
 #define PHASE_PROLOGUE(MAP)                                                                                             \
   extern __shared__ __align__(16) unsigned char smem_raw[];                                                              \
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;                                                            \
-  const int env = a.env0 + blockIdx.x * WPB + warp;                                                                      \
+  const int env = a.env0 + blockIdx.x * MAP::W + warp;                                                                      \
   if (env >= a.env1) return;                      /* no block-wide barrier anywhere in a phase kernel */                 \
   if (a.mask && !a.mask[env]) return;                                                                                    \
   T* sm_ = reinterpret_cast<T*>(smem_raw) + (size_t)warp * map_st<MAP>();                                                \
-  int* smi_ = reinterpret_cast<int*>(smem_raw + (size_t)WPB * map_st<MAP>() * sizeof(T)) + warp * map_si<MAP>();         \
+  int* smi_ = reinterpret_cast<int*>(smem_raw + (size_t)MAP::W * map_st<MAP>() * sizeof(T)) + warp * map_si<MAP>();      \
   Ctx<T, MAP> c(m, sm_, smi_, st.ctx + (size_t)env * CTX_T, st.ctxi + (size_t)env * CTX_I, lane);                        \
   /* one mbarrier per warp (byte count of its bulk stage-in copies) behind the maps, inside the dynamic allocation */   \
-  unsigned long long* bar_ = reinterpret_cast<unsigned long long*>(smem_raw + (size_t)WPB * map_bytes<T, MAP>()) + 2 * warp; \
+  unsigned long long* bar_ = reinterpret_cast<unsigned long long*>(smem_raw + (size_t)MAP::W * map_bytes<T, MAP>()) + 2 * warp; \
   stage_in(c, bar_);                                                                                                     \
   __syncwarp();
 
@@ -228,22 +238,23 @@ __global__ void __launch_bounds__(WPB * 32) reset_kernel(const __grid_constant__
 }
 
 // ---------------------------------------------------------------- phase 3: constraint rows + Newton
-// MC = MAXCON_S: envs with ncon <= MAXCON_S; MC = MAXCON: the others (see MapSolveT).  The small class is compiled for
-// 5 blocks per SM (<= 102 registers), which its shared-memory slice allows.
+// MC = MAXCON_S: envs with ncon <= MAXCON_S; MC = MAXCON: the others (see MapSolveT).  The small class runs 4 blocks of
+// 5 envs per SM (<= 102 registers), its warps in block-lockstep through the Newton iteration (constraint.cuh: newton).
 #ifndef ADROIT_SOLVE_BLOCKS
-#define ADROIT_SOLVE_BLOCKS 5
+#define ADROIT_SOLVE_BLOCKS 4
 #endif
 template <typename T, int MC>
-__global__ void __launch_bounds__(WPB * 32, (MC < MAXCON && sizeof(T) == 4) ? ADROIT_SOLVE_BLOCKS : 1)
+__global__ void __launch_bounds__(MapSolveK<T, MC>::W * 32, (MC < MAXCON && sizeof(T) == 4) ? ADROIT_SOLVE_BLOCKS : 1)
     solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, const __grid_constant__ PArgs a) {
   PDL_WAIT()
   if (MAXCON_S < MAXCON) {
-    const int env_ = a.env0 + blockIdx.x * WPB + (threadIdx.x >> 5);
+    const int env_ = a.env0 + blockIdx.x * MapSolveK<T, MC>::W + (threadIdx.x >> 5);
     if (env_ >= a.env1) return;
     const bool small = st.ctxi[(size_t)env_ * CTX_I + SM_I + GI_NCON] <= MAXCON_S;
     if (small != (MC < MAXCON)) return;
   }
-  PHASE_PROLOGUE(MapSolveT<MC>)
+  using MapK = MapSolveK<T, MC>;
+  PHASE_PROLOGUE(MapK)
   c.ncon = c.gi[GI_NCON];
   make_constraint(c, st.overflow);
   newton(c);
@@ -633,6 +644,12 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
   // stash offsets; pointers are patched once the arena is on the device
   for (auto& f : fix) *f.slot = (const void*)f.off;
 
+  {
+    auto td = B.ints("tendon_dof");
+    auto tc = B.reals("tendon_coef");
+    if (m.ntendon > MAXTENDON || (int)td.size() < 2 * m.ntendon || (int)tc.size() < 2 * m.ntendon) throw std::string("more fixed tendons than model.cuh's MAXTENDON");
+    for (int i = 0; i < 2 * MAXTENDON; i++) { m.tdof[i] = i < 2 * m.ntendon ? td[i] : -1; m.tcoef[i] = i < 2 * m.ntendon ? (T)tc[i] : T(0); }
+  }
   auto ti = B.ints("task_int", 16);
   for (int i = 0; i < 16; i++) m.task_int[i] = ti[i];
   auto par0 = B.reals("par0");
@@ -688,13 +705,14 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
   return 0;
 }
 
+static int g_extra_smem_solve = 0;   // ADROIT_EXTRA_SMEM_SOLVE: bytes of unused dynamic shared memory added to the solve launches
 // dynamic shared memory of a phase kernel: the WPB map slices + 16 bytes per warp for its stage-in mbarrier
-template <typename T, class MAP> constexpr size_t phase_smem() { return WPB * map_bytes<T, MAP>() + WPB * 16; }
+template <typename T, class MAP> constexpr size_t phase_smem() { return MAP::W * map_bytes<T, MAP>() + MAP::W * 16; }
 
 template <typename T, class MAP, typename K>
 int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {
-  size_t smem = phase_smem<T, MAP>();
-  int blocks = (a.env1 - a.env0 + WPB - 1) / WPB;
+  size_t smem = phase_smem<T, MAP>() + (phase == 2 ? g_extra_smem_solve : 0);   // (occupancy experiments, tools/gpu_occ_sweep.sh)
+  int blocks = (a.env1 - a.env0 + MAP::W - 1) / MAP::W;
   if (blocks <= 0) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (s->profile) {
@@ -705,14 +723,14 @@ int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const D
   if (s->pdl) {
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(WPB * 32); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(MAP::W * 32); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     CK(cudaLaunchKernelEx(&cfg, kernel, m, st, a));
   } else {
-    kernel<<<blocks, WPB * 32, smem, stream>>>(m, st, a);
+    kernel<<<blocks, MAP::W * 32, smem, stream>>>(m, st, a);
     CK(cudaGetLastError());
   }
   if (s->profile) {
@@ -725,10 +743,11 @@ int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const D
 }
 
 template <typename T> int configure_kernels() {
+  { const char* e = getenv("ADROIT_EXTRA_SMEM_SOLVE"); g_extra_smem_solve = e ? atoi(e) : 0; }
   CK(cudaFuncSetAttribute(smooth_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSmooth>()));
   CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapCollide>()));
-  CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolve>()));
-  if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveS>()));
+  CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON>>() + g_extra_smem_solve));
+  if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON_S>>() + g_extra_smem_solve));
   CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapFinish>()));
   CK(cudaFuncSetAttribute(reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapReset>()));
   return 0;
@@ -738,8 +757,8 @@ template <typename T> int configure_kernels() {
 template <typename T> int forward_pass(adroit_sim* s, const DModel<T>& m, const DState<T>& st, PArgs a, cudaStream_t stream) {
   if (launch_phase<T, MapSmooth>(s, 0, smooth_kernel<T>, m, st, a, stream)) return 1;
   if (launch_phase<T, MapCollide>(s, 1, collide_kernel<T>, m, st, a, stream)) return 1;
-  if (MAXCON_S < MAXCON && launch_phase<T, MapSolveS>(s, 2, solve_kernel<T, MAXCON_S>, m, st, a, stream)) return 1;
-  if (launch_phase<T, MapSolve>(s, 2, solve_kernel<T, MAXCON>, m, st, a, stream)) return 1;
+  if (MAXCON_S < MAXCON && launch_phase<T, MapSolveK<T, MAXCON_S>>(s, 2, solve_kernel<T, MAXCON_S>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapSolveK<T, MAXCON>>(s, 2, solve_kernel<T, MAXCON>, m, st, a, stream)) return 1;
   if (launch_phase<T, MapFinish>(s, 3, finish_kernel<T>, m, st, a, stream)) return 1;
   return 0;
 }
@@ -802,8 +821,9 @@ int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, cons
   memset(&a, 0, sizeof a);
   a.debug = debug;
   int nsub = (s->profile || debug) ? 1 : s->nsub;
-  int per = ((st.n + nsub - 1) / nsub + WPB - 1) / WPB * WPB;
-  if (per < 64 * WPB) { per = 64 * WPB; }          // never less than 64 blocks per launch
+  constexpr int EA = WPB * ADROIT_WPB_SOLVE;        // sub-batch boundaries fall on block boundaries of every phase kernel
+  int per = ((st.n + nsub - 1) / nsub + EA - 1) / EA * EA;
+  if (per < 64 * WPB) { per = (64 * WPB + EA - 1) / EA * EA; }          // never less than 64 blocks per launch
   nsub = (st.n + per - 1) / per;
   if (nsub <= 1) {
     a.env0 = 0; a.env1 = st.n;
@@ -1161,8 +1181,8 @@ int adroit_debug_layout(int* out, int max_n) {
   const int v[] = {NVP, NBP, NGP, NSP, MAXCON, CROWS, NTRI, NPARP, NTF, G_TOTAL, GI_TOTAL, G_GPOS, G_GMAT, G_SPOS, G_CON, G_JR, G_MINV,
                    G_DBG_M, G_DBG_BIAS, G_DBG_QFS, G_DBG_QAS, G_DBG_QACC, G_DBG_QFC, G_DBG_XPOS, G_DBG_XQUAT, G_DBG_EF, GI_CON,
                    // dynamic shared memory per block of the fp32 phase kernels (occupancy bookkeeping, tools/occupancy.py)
-                   (int)phase_smem<float, MapSmooth>(), (int)phase_smem<float, MapCollide>(), (int)phase_smem<float, MapSolveS>(),
-                   (int)phase_smem<float, MapSolve>(), (int)phase_smem<float, MapFinish>(), (int)phase_smem<float, MapReset>(), CTX_T, CTX_I};
+                   (int)phase_smem<float, MapSmooth>(), (int)phase_smem<float, MapCollide>(), (int)phase_smem<float, MapSolveK<float, MAXCON_S>>(),
+                   (int)phase_smem<float, MapSolveK<float, MAXCON>>(), (int)phase_smem<float, MapFinish>(), (int)phase_smem<float, MapReset>(), CTX_T, CTX_I};
   int n = (int)(sizeof v / sizeof v[0]);
   for (int i = 0; i < n && i < max_n; i++) out[i] = v[i];
   return n;

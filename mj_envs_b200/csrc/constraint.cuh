@@ -223,8 +223,8 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
     if (t < m.ntendon && m.tendon_limited[t]) {
       T len = 0;
       for (int k = 0; k < 2; k++) {
-        int dj = m.tendon_dof[2 * t + k];
-        if (dj >= 0) { len += m.tendon_coef[2 * t + k] * qpos[dj]; vel += m.tendon_coef[2 * t + k] * qvel[dj]; }
+        int dj = m.tdof[2 * t + k];
+        if (dj >= 0) { len += m.tcoef[2 * t + k] * qpos[dj]; vel += m.tcoef[2 * t + k] * qvel[dj]; }
       }
       dist = up ? m.tendon_range[2 * t + 1] - len : len - m.tendon_range[2 * t];
       has = dist < m.tendon_margin[t];
@@ -345,8 +345,8 @@ template <typename T> DI T simple_dot(const DModel<T>& m, int info, const T* x) 
   if (kind == S_JLIMIT) return up ? -x[id] : x[id];
   T s = 0;
   for (int k = 0; k < 2; k++) {
-    int dj = m.tendon_dof[2 * id + k];
-    if (dj >= 0) s += m.tendon_coef[2 * id + k] * x[dj];
+    int dj = m.tdof[2 * id + k];
+    if (dj >= 0) s += m.tcoef[2 * id + k] * x[dj];
   }
   return up ? -s : s;
 }
@@ -463,8 +463,8 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
       else if (kind == S_JLIMIT) atomicAdd(qfc + id, up ? -f : f);
       else
         for (int k = 0; k < 2; k++) {
-          int dj = m.tendon_dof[2 * id + k];
-          if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tendon_coef[2 * id + k]);
+          int dj = m.tdof[2 * id + k];
+          if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tcoef[2 * id + k]);
         }
     }
   }
@@ -601,8 +601,8 @@ template <class CX> PHASE_FN void build_hessian(CX& c) {
     T D = sD[r];
     if (kind != S_TLIMIT) atomicAdd(H + tri(id, id), D);
     else {
-      int d0 = m.tendon_dof[2 * id], d1 = m.tendon_dof[2 * id + 1];
-      T c0 = m.tendon_coef[2 * id], c1 = m.tendon_coef[2 * id + 1];
+      int d0 = m.tdof[2 * id], d1 = m.tdof[2 * id + 1];
+      T c0 = m.tcoef[2 * id], c1 = m.tcoef[2 * id + 1];
       if (d0 >= 0) atomicAdd(H + tri(d0, d0), D * c0 * c0);
       if (d1 >= 0) atomicAdd(H + tri(d1, d1), D * c1 * c1);
       if (d0 >= 0 && d1 >= 0) atomicAdd(H + (d0 > d1 ? tri(d0, d1) : tri(d1, d0)), D * c0 * c1);
@@ -657,7 +657,7 @@ template <class CX> PHASE_FN void build_hessian(CX& c) {
 #define ADROIT_STOP_ON_QUADRATIC 1
 #endif
 #ifndef ADROIT_LOCKSTEP
-#define ADROIT_LOCKSTEP 0
+#define ADROIT_LOCKSTEP 2   // 0 = free-running warps, 1 = block barrier per Newton iteration, 2 = block barrier per sub-phase (measured: +10 % hammer)
 #endif
 // ---------------------------------------------------------------- Newton solver (primal, exact line search)
 template <class CX> PHASE_FN void newton(CX& c) {
@@ -695,6 +695,85 @@ template <class CX> PHASE_FN void newton(CX& c) {
   int iters = 0;
   bool refactor = true;
   bool done = false;
+#if ADROIT_LOCKSTEP == 2
+  // Block-lockstep Newton: the warps of a block walk the iteration in the same order of sub-phases with a block barrier
+  // between them, so that the SM's instruction cache holds ONE sub-phase's code at a time instead of every warp's own
+  // position in the ~60 KB loop (at full occupancy the kernel stalls 3.4 cycles per issued instruction on instruction
+  // fetch, profiles/R2c_solve_hammer_full.summary.txt).  A warp whose env has converged idles at the barriers until the
+  // block's last env is done.  Arithmetic and its order are those of the free-running loop.
+  for (int iter = 0; iter < m.iterations; iter++) {
+    if (!__syncthreads_or(!done)) break;
+    bool act = !done;
+    done = true;
+    if (act) {
+      T g2 = 0;
+      _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) {
+        T g = Ma[j] - qfs[j] - qfc[j];
+        grad[j] = g;
+        search[j] = -g;
+        g2 += g * g;
+      }
+      g2 = warp_sum(g2);
+      if (scale * sqrt(g2) < m.tolerance) act = false;
+    }
+    if (act && refactor) build_hessian(c);
+    __syncthreads();
+    if (act && refactor) chol_dense(H, c.template V<V_DINV>(), grad, Mv, nv, lane);
+    __syncthreads();
+    if (act) {
+      chol_solve(H, c.template V<V_DINV>(), search, nv, lane);
+      symv(M, search, Mv, nv, lane);
+      contact_frame_mul(c, search, av);
+      __syncwarp();
+    }
+    __syncthreads();
+    T alpha = 0;
+    if (act) {
+      T A0 = 0, B0 = 0;
+      _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) { A0 += search[j] * Mv[j]; B0 += search[j] * (Ma[j] - qfs[j]); }
+      A0 = warp_sum(A0);
+      B0 = warp_sum(B0);
+      T d1, d2;
+      LsRows<T> R;
+      ls_prepare(c, qacc, search, R);
+      ls_eval(R, T(0), d1, d2);
+      T f1 = B0 + d1, f2 = A0 + d2;
+      if (f1 < 0) {
+        const T gtol = (sizeof(T) == 4 ? T(1e-6) : T(1e-13)) * (-f1);
+        T lo = 0, hi = -1;  // hi < 0: unbounded
+        alpha = -f1 / f2;
+        for (int it = 0; it < 40; it++) {
+          ls_eval(R, alpha, d1, d2);
+          T fa = A0 * alpha + B0 + d1, fb = A0 + d2;
+          if (tabs(fa) <= gtol) break;
+          if (fa < 0) lo = alpha; else hi = alpha;
+          T nxt = alpha - fa / fb;
+          bool inside = nxt > lo && (hi < 0 || nxt < hi);
+          if (!inside) nxt = hi < 0 ? 2 * alpha : T(0.5) * (lo + hi);
+          if (hi >= 0 && (hi - lo) <= (sizeof(T) == 4 ? T(1e-7) : T(1e-15)) * hi) { alpha = nxt; break; }
+          alpha = nxt;
+        }
+      }
+      if (alpha == 0) act = false;
+    }
+    __syncthreads();
+    if (act) {
+      _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) { qacc[j] += alpha * search[j]; Ma[j] += alpha * Mv[j]; }
+      _Pragma("unroll 1") for (int r = lane; r < 4 * c.ncon; r += 32) ac[r] += alpha * av[r];
+      __syncwarp();
+      T old = cost;
+      cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
+      refactor = c.nchanged != 0;
+      iters = iter + 1;
+      T floor_ = sizeof(T) == 4 ? T(2e-6) * tabs(cost) : T(0);
+      bool stop = scale * (old - cost) < m.tolerance || (old - cost) < floor_;
+#if ADROIT_STOP_ON_QUADRATIC
+      stop = stop || (!refactor && !c.nflipped);
+#endif
+      if (!stop) done = false;
+    }
+  }
+#else
   for (int iter = 0; iter < m.iterations; iter++) {
 #if ADROIT_LOCKSTEP
     // the warps of a block enter every Newton iteration together: one instruction-cache working set per block
@@ -769,6 +848,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     done = false;
     } while (0);
   }
+#endif
   if (lane == 0) c.gi[GI_NITER] = iters;
 }
 
@@ -935,8 +1015,8 @@ template <class CX> PHASE_FN void constraint_force(CX& c) {
     else if (kind == S_JLIMIT) atomicAdd(qfc + id, up ? -f : f);
     else
       for (int k = 0; k < 2; k++) {
-        int dj = m.tendon_dof[2 * id + k];
-        if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tendon_coef[2 * id + k]);
+        int dj = m.tdof[2 * id + k];
+        if (dj >= 0) atomicAdd(qfc + dj, (up ? -f : f) * m.tcoef[2 * id + k]);
       }
   }
   frame_forces(c, F);

@@ -25,6 +25,7 @@ constexpr int MAXSIMPLE = ADROIT_MAXSIMPLE;  // friction-loss + joint-limit + te
 constexpr int NTRI = ADROIT_NTRI;      // lower triangle of a 36x36 matrix, rows padded to multiples of 4 (16-byte aligned rows, see tri())
 constexpr int NPARP = 8;       // per-env model parameters (board_pos | door_body_pos | target quat | obj pos + target pos)
 constexpr int NTF = 24;        // cached task frames (positions the observation / reward read)
+constexpr int MAXTENDON = 48;  // fixed tendons (Adroit: 44, all limited; at most two joints each)
 #ifndef ADROIT_WPB
 #define ADROIT_WPB 4
 #endif
@@ -126,6 +127,9 @@ template <typename T> struct DModel {
   const int* render_int;                             // [nrender][4] type, body, par offset of the local pos (-1), is_site
   const T* render_real;                              // [nrender][19] local pos, local mat, size, rgba (render.cuh)
   int task_int[16];
+  // fixed-tendon tables by value: kernel-parameter (constant-bank) reads instead of L2 round trips on the row loops' chain
+  int tdof[2 * MAXTENDON];
+  T tcoef[2 * MAXTENDON];
   T par0[NPARP];
   T touch_size[3];
   T timestep, gravity[3], tolerance, noslip_tolerance, impratio, solref[2], solimp[5], mpr_tolerance, meaninertia;
