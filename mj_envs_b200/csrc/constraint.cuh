@@ -176,7 +176,7 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
   sol_KB(m, K, B);
   int nrow = 0, dropped = 0;
   // friction loss (one row per dof with frictionloss > 0)
-  for (int base = 0; base < m.nv; base += 32) {
+  _Pragma("unroll 1") for (int base = 0; base < m.nv; base += 32) {
     int j = base + c.lane;
     bool has = j < m.nv && m.dof_frictionloss[j] > 0;
     unsigned mask = __ballot_sync(0xffffffffu, has);
@@ -193,7 +193,7 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
     nrow += __popc(mask);
   }
   // joint limits: q = 2*j + (upper side)
-  for (int base = 0; base < 2 * m.nv; base += 32) {
+  _Pragma("unroll 1") for (int base = 0; base < 2 * m.nv; base += 32) {
     int q = base + c.lane, j = q >> 1, up = q & 1;
     bool has = false;
     T dist = 0;
@@ -216,7 +216,7 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
     nrow += __popc(mask);
   }
   // tendon limits
-  for (int base = 0; base < 2 * m.ntendon; base += 32) {
+  _Pragma("unroll 1") for (int base = 0; base < 2 * m.ntendon; base += 32) {
     int q = base + c.lane, t = q >> 1, up = q & 1;
     bool has = false;
     T dist = 0, vel = 0;
@@ -352,8 +352,11 @@ template <typename T> DI T simple_dot(const DModel<T>& m, int info, const T* x) 
 }
 // contact-frame products  out[ci][a] = Jf[ci][a] . x   (lanes over dofs: coalesced row reads, the four rows of a
 // contact reduced together)
-template <class CX> SUB_FN void contact_frame_mul(CX& c, const typename CX::real* x, typename CX::real* out) {
+template <class CX> SUB_FN void contact_frame_mul(CX c, const typename CX::real* x, typename CX::real* out) {
   using T = typename CX::real;
+  assume_spaces(c);
+  __builtin_assume(__isShared(x));
+  __builtin_assume(__isShared(out));
   const T* JR = c.template G<G_JR>();
   const int nv = c.m.nv, lane = c.lane;
   const bool hi = nv > 32 && lane < NVP - 32;
@@ -429,8 +432,11 @@ template <class CX> DI void add_jt_force(CX& c, const typename CX::real* F, type
 
 // cost, forces and states at the point whose frame accelerations are in O_AC and dof accelerations in `qacc`.
 // Returns the constraint cost (all lanes).  Also accumulates J^T f into V_QFC when `want_qfc`.
-template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const typename CX::real* qacc, bool want_qfc) {
+template <typename T> struct CuResult { T cost; int nchanged, nflipped; };
+template <class CX> SUB_FN CuResult<typename CX::real> constraint_update_fn(CX c, const typename CX::real* qacc, bool want_qfc) {
   using T = typename CX::real;
+  assume_spaces(c);
+  __builtin_assume(__isShared(qacc));
   const DModel<T>& m = c.m;
   int* sinfo = c.template I<I_SINFO>();
   const T *sD = c.template S<O_SD>(), *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>();
@@ -514,23 +520,36 @@ template <class CX> SUB_FN typename CX::real constraint_update(CX& c, const type
     add_jt_force(c, F, qfc);
     __syncwarp();
   }
-  return warp_sum(cost);
+  CuResult<T> res;
+  res.cost = warp_sum(cost);
+  res.nchanged = c.nchanged;
+  res.nflipped = c.nflipped;
+  return res;
+}
+template <class CX> DI typename CX::real constraint_update(CX& c, const typename CX::real* qacc, bool want_qfc) {
+  CuResult<typename CX::real> r = constraint_update_fn(c, qacc, want_qfc);
+  c.nchanged = r.nchanged;
+  c.nflipped = r.nflipped;
+  return r.cost;
 }
 
 // Exact line search support.  Along qacc + alpha*search every row's residual is x + alpha*y; x, y and the row
 // constants are computed ONCE per Newton iteration into registers (lane l owns simple rows l, l+32, l+64 and pyramid
 // edges l, l+32, ..., l+160), so that evaluating (f', f'') at a new alpha is pure register arithmetic + two warp sums.
-template <typename T> struct LsRows {
-  T xs[3], ys[3], Ds[3], fs[3], rf[3];   // simple rows: D = 0 marks an absent row, fs < 0 a one-sided (limit) row
-  T xe[6], ye[6], De[6];                 // pyramid edges
+// NE = register sets for the pyramid edges of this kernel's contact capacity (3 for the 16-contact class, 6 for 32)
+constexpr int NS_LS = (MAXSIMPLE + 31) / 32;
+template <typename T, int NE> struct LsRows {
+  T xs[NS_LS], ys[NS_LS], Ds[NS_LS], fs[NS_LS], rf[NS_LS];   // simple rows: D = 0 marks an absent row, fs < 0 a one-sided (limit) row
+  T xe[NE], ye[NE], De[NE];                                   // pyramid edges
 };
-template <class CX> DI void ls_prepare(CX& c, const typename CX::real* qacc, const typename CX::real* search, LsRows<typename CX::real>& R) {
+template <class CX> constexpr int ls_sets() { return (6 * (CX::MCAP < 32 ? CX::MCAP : 32) + 31) / 32; }
+template <class CX> DI void ls_prepare(CX& c, const typename CX::real* qacc, const typename CX::real* search, LsRows<typename CX::real, ls_sets<CX>()>& R) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
   const int* sinfo = c.template I<I_SINFO>();
   const T *sD = c.template S<O_SD>(), *saref = c.template S<O_SAREF>(), *sfl = c.template S<O_SFL>();
 #pragma unroll
-  for (int q = 0; q < 3; q++) {
+  for (int q = 0; q < NS_LS; q++) {
     int r = c.lane + 32 * q;
     R.Ds[q] = 0; R.xs[q] = 0; R.ys[q] = 0; R.fs[q] = -1; R.rf[q] = 0;
     if (r < c.nsimple) {
@@ -546,7 +565,7 @@ template <class CX> DI void ls_prepare(CX& c, const typename CX::real* qacc, con
   const T *carefn = c.template S<O_CAREFN>(), *cbt = c.template S<O_CBT>();
   const int* cdim = c.template I<I_CDIM>();
 #pragma unroll
-  for (int q = 0; q < 6; q++) {
+  for (int q = 0; q < ls_sets<CX>(); q++) {
     int t = c.lane + 32 * q;
     R.De[q] = 0; R.xe[q] = 0; R.ye[q] = 0;
     if (t < 6 * c.ncon) {
@@ -563,10 +582,10 @@ template <class CX> DI void ls_prepare(CX& c, const typename CX::real* qacc, con
   }
 }
 // derivative pair (f', f'') of the constraint cost at alpha
-template <typename T> DI void ls_eval(const LsRows<T>& R, T alpha, T& d1, T& d2) {
+template <typename T, int NE> DI void ls_eval(const LsRows<T, NE>& R, T alpha, T& d1, T& d2) {
   T a = 0, b = 0;
 #pragma unroll
-  for (int q = 0; q < 3; q++) {
+  for (int q = 0; q < NS_LS; q++) {
     T D = R.Ds[q], y = R.ys[q], z = R.xs[q] + alpha * y;
     if (D > 0) {
       if (R.fs[q] >= 0) {
@@ -577,7 +596,7 @@ template <typename T> DI void ls_eval(const LsRows<T>& R, T alpha, T& d1, T& d2)
     }
   }
 #pragma unroll
-  for (int q = 0; q < 6; q++) {
+  for (int q = 0; q < NE; q++) {
     T D = R.De[q], y = R.ye[q], z = R.xe[q] + alpha * y;
     if (D > 0 && z < 0) { a += D * z * y; b += D * y * y; }
   }
@@ -679,7 +698,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
   contact_frame_mul(c, qas, ac);
   __syncwarp();
   T cost_sm = constraint_update(c, qas, false);
-  symv(M, warm, Ma, nv, lane);
+  symv<T, true, true>(M, warm, Ma, nv, lane);
   contact_frame_mul(c, warm, ac);
   __syncwarp();
   T cost = constraint_update(c, warm, true) + gauss(warm, Ma);
@@ -687,7 +706,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
   _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) qacc[j] = use_ws ? warm[j] : qas[j];
   __syncwarp();
   if (!use_ws) {
-    symv(M, qacc, Ma, nv, lane);
+    symv<T, true, true>(M, qacc, Ma, nv, lane);
     contact_frame_mul(c, qacc, ac);
     __syncwarp();
     cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
@@ -722,7 +741,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     __syncthreads();
     if (act) {
       chol_solve(H, c.template V<V_DINV>(), search, nv, lane);
-      symv(M, search, Mv, nv, lane);
+      symv<T, true, true>(M, search, Mv, nv, lane);
       contact_frame_mul(c, search, av);
       __syncwarp();
     }
@@ -734,7 +753,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
       A0 = warp_sum(A0);
       B0 = warp_sum(B0);
       T d1, d2;
-      LsRows<T> R;
+      LsRows<T, ls_sets<CX>()> R;
       ls_prepare(c, qacc, search, R);
       ls_eval(R, T(0), d1, d2);
       T f1 = B0 + d1, f2 = A0 + d2;
@@ -798,7 +817,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
       chol_dense(H, c.template V<V_DINV>(), grad, Mv, nv, lane);   // grad / Mv: free at this point (column broadcast buffers)
     }
     chol_solve(H, c.template V<V_DINV>(), search, nv, lane);
-    symv(M, search, Mv, nv, lane);
+    symv<T, true, true>(M, search, Mv, nv, lane);
     contact_frame_mul(c, search, av);
     __syncwarp();
     // exact line search on the convex piecewise-quadratic: safeguarded Newton on f'(alpha)
@@ -807,7 +826,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     A0 = warp_sum(A0);
     B0 = warp_sum(B0);
     T d1, d2;
-    LsRows<T> R;
+    LsRows<T, ls_sets<CX>()> R;
     ls_prepare(c, qacc, search, R);
     ls_eval(R, T(0), d1, d2);
     T f1 = B0 + d1, f2 = A0 + d2;

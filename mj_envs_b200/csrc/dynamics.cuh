@@ -41,6 +41,11 @@ template <class MAP> constexpr int map_ioff(int O) {
   }
   return -1;
 }
+// length of the map's region that starts at context offset O (-1: the region is not staged)
+template <class MAP> constexpr int map_rlen(int O) {
+  for (int i = 0; i < MAP::NT; i++) if (MAP::RT[i].off == O) return MAP::RT[i].len;
+  return -1;
+}
 template <class MAP> constexpr int map_st() { int a = 0; for (int i = 0; i < MAP::NT; i++) a += pad4(MAP::RT[i].len); return a; }
 template <class MAP> constexpr int map_si() { int a = 0; for (int i = 0; i < MAP::NI; i++) a += pad4(MAP::RI[i].len); return a; }
 template <typename T, class MAP> constexpr size_t map_bytes() { return map_st<MAP>() * sizeof(T) + map_si<MAP>() * sizeof(int); }
@@ -59,6 +64,8 @@ template <typename T_, class MAP_> struct Ctx {
   int ncon, nsimple, nchanged, nflipped;
   __device__ Ctx(const DModel<T>& mm, T* sm_, int* smi_, T* gb_, int* gib_, int lane_)
       : m(mm), sm(sm_), smi(smi_), gb(gb_), gib(gib_), gi(gib_ + SM_I), lane(lane_), ncon(0), nsimple(0), nchanged(1), nflipped(0) {}
+  // contact capacity of this kernel's shared-memory tables (the size class of the solve kernel), MAXCON if they are not staged
+  static constexpr int MCAP = map_rlen<MAP>(O_AC) > 0 ? map_rlen<MAP>(O_AC) / 4 : MAXCON;
   template <int O> static constexpr bool in_smem() { return map_soff<MAP>(O) >= 0; }
   template <int O> DI T* S() const {
     constexpr int so = map_soff<MAP>(O);
@@ -73,6 +80,17 @@ template <typename T_, class MAP_> struct Ctx {
     else return gib + O;
   }
 };
+
+// Address-space hints for the few `SUB_FN` (noinline) helpers: they receive the Ctx BY VALUE (a reference would make the
+// caller's Ctx escape to local memory, after which every access in the caller is a generic load with 64-bit address
+// arithmetic -- 252 generic LD/ST sites and 90 LDL/STL in the round-1 solve kernel) and state what the pointers are.
+template <class CX> DI void assume_spaces(const CX& c) {
+  __builtin_assume(__isShared(c.sm));
+  __builtin_assume(__isShared(c.smi));
+  __builtin_assume(__isGlobal(c.gb));
+  __builtin_assume(__isGlobal(c.gib));
+  __builtin_assume(__isGlobal(c.gi));
+}
 
 // stage the MAP's regions between the context block and shared memory.
 //
@@ -935,9 +953,39 @@ template <typename T> PHASE_FN void minv_tree(const DModel<T>& m, T* L, const T*
 }
 
 // y = A x for a symmetric matrix (lower storage); x, y in shared memory, y != x
-template <typename T> SUB_FN void symv(const T* A, const T* x, T* y, int n, int lane) {
+// COMPACT: rolled loops (the solve kernel is instruction-fetch bound: 1.5 KB of code instead of 6 KB)
+// SH: A, x and y are all in shared memory (the solve kernel); otherwise A and x are, y may be anywhere
+template <typename T, bool COMPACT = false, bool SH = false> SUB_FN void symv(const T* A, const T* x, T* y, int n, int lane) {
+  __builtin_assume(__isShared(A));
+  __builtin_assume(__isShared(x));
+  if constexpr (SH) __builtin_assume(__isShared(y));
   T y0 = 0, y1 = 0;
   const int i0 = lane, i1 = lane + 32;
+  if constexpr (COMPACT) {
+    if (i0 < n) {
+      const T* r = A + rowoff(i0);
+      _Pragma("unroll 1") for (int k = 0; k <= i0; k += 4) {
+        Vec4<T> a = ld4(r + k), b = ld4(x + k);
+        y0 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
+      }
+    }
+    if (i1 < n) {
+      const T* r = A + rowoff(i1);
+      _Pragma("unroll 1") for (int k = 0; k <= i1; k += 4) {
+        Vec4<T> a = ld4(r + k), b = ld4(x + k);
+        y1 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
+      }
+    }
+    _Pragma("unroll 2") for (int j = 1; j < n; j++) {
+      const T* rj = A + rowoff(j);
+      T xj = x[j];
+      if (i0 < j) y0 += rj[i0] * xj;
+      if (j > 32 && i1 < j) y1 += rj[i1] * xj;
+    }
+    if (i0 < n) y[i0] = y0;
+    if (i1 < n) y[i1] = y1;
+    return;
+  }
   if (i0 < n) {
     const T* r = A + rowoff(i0);
     for (int k = 0; k <= i0; k += 4) {      // pad entries of the row are zero
