@@ -41,14 +41,17 @@ struct PArgs {
 
 #define VR(V, F) Reg{(V) * NVP, NVP, (F)}
 // ---- shared-memory maps of the phase kernels (everything not listed is addressed in the context block directly)
+#ifndef ADROIT_WPB_SMOOTH
+#define ADROIT_WPB_SMOOTH ADROIT_WPB
+#endif
 struct MapSmooth {
-  static constexpr int W = WPB;   // warps (= envs) per block of the kernel that uses this map
-  static constexpr int NT = 17, NI = 1;
+  static constexpr int W = ADROIT_WPB_SMOOTH;   // warps (= envs) per block of the kernel that uses this map
+  static constexpr int NT = 16, NI = 1;
   static constexpr Reg RT[NT] = {VR(V_CTRL, R_IN | R_OUT), VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_QFS, R_ZERO | R_OUT),
                                  VR(V_QAS, R_ZERO | R_OUT), VR(V_T1, R_ZERO), VR(V_T2, R_ZERO), VR(V_DINV, R_ZERO),
                                  Reg{O_PAR, NPARP, R_IN | R_OUT}, Reg{O_XPOS, NBP * 3, R_OUT}, Reg{O_XQUAT, NBP * 4, R_OUT},
                                  Reg{O_XMAT, NBP * 9, R_OUT}, Reg{O_XANC, NVP * 3, R_OUT}, Reg{O_XAXIS, NVP * 3, R_OUT},
-                                 Reg{O_CRB, NBP * 10, 0}, Reg{O_M, NTRI, R_OUT}, Reg{O_H, NTRI, 0}};
+                                 Reg{O_CRB, NBP * 10, 0}, Reg{O_M, NTRI, 0}};   // M: stored early by the kernel itself, then factored in place
   static constexpr Reg RI[NI] = {Reg{I_SURV, 4, 0}};
 };
 // the geom frames (written by the smooth kernel) are staged: the broad phase walks ~250 candidate pairs per env and
@@ -175,7 +178,7 @@ template <class C, typename T> DI void reset_prologue(C& c, const DModel<T>& m, 
 // ---------------------------------------------------------------- phase 1: smooth dynamics
 // [reset_model prologue] [action map] [mj_checkPos/Vel] kinematics, frames, CRB, RNE, actuation, L^T D L, qacc_smooth, M^-1
 template <typename T>
-__global__ void __launch_bounds__(WPB * 32) smooth_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+__global__ void __launch_bounds__(MapSmooth::W * 32) smooth_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                            const __grid_constant__ PArgs a) {
   PDL_WAIT()
   PHASE_PROLOGUE(MapSmooth)
@@ -193,6 +196,7 @@ __global__ void __launch_bounds__(WPB * 32) smooth_kernel(const __grid_constant_
   if (a.check && (warp_bad(c.template V<V_QPOS>(), nv, lane) || warp_bad(c.template V<V_QVEL>(), nv, lane))) zero_state(c);  // mj_checkPos / mj_checkVel
   kinematics(c);
   frames_and_inertia(c);
+  rne_bias(c);            // (its body-vector scratch lives where M is about to be built)
   mass_matrix(c);
   if (a.debug) {
     const T* M = c.template S<O_M>();
@@ -202,15 +206,20 @@ __global__ void __launch_bounds__(WPB * 32) smooth_kernel(const __grid_constant_
       if (j <= i) D[(i * (i + 1)) / 2 + j] = M[tri(i, j)];
     }
   }
-  rne_bias(c);
+  // M leaves for the context block now (one bulk copy, the solve and finish kernels read it); the same shared-memory
+  // region then holds its factor: no second 2.9 KB matrix per env, one more resident block per SM
+  store_region_early<O_M, NTRI>(c);
   smooth_dynamics(c, m.noslip_iterations > 0);
   __syncwarp();
   stage_out(c);
 }
 
 // ---------------------------------------------------------------- phase 2: collision
+#ifndef ADROIT_COLLIDE_BLOCKS
+#define ADROIT_COLLIDE_BLOCKS 3   // <= 168 registers: 3 blocks per SM instead of 2 at 202 (collide -11 % hammer, -7.5 % pen; 4 blocks at 128 registers: slower)
+#endif
 template <typename T>
-__global__ void __launch_bounds__(WPB * 32) collide_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+__global__ void __launch_bounds__(WPB * 32, ADROIT_COLLIDE_BLOCKS) collide_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                             const __grid_constant__ PArgs a) {
   PDL_WAIT()
   PHASE_PROLOGUE(MapCollide)
@@ -603,6 +612,44 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
       while (wl_pair.size() % 32) wl_pair.push_back(-1);
     }
     m.n_wl = (int)wl_pair.size();
+    {  // level-scheduled L^T D L program (dynamics.cuh: ltdl_factor): dofs of equal depth are eliminated together, deepest level
+       // first; within a level the (ancestor, ancestor) updates are split into rounds whose targets are all different (dofs
+       // of different fingers share the arm / wrist ancestors), so a round is plain load-FMA-store with no atomics and the
+       // summation order is fixed
+      auto toff = [](int i, int j) { if (i < j) { int t = i; i = j; j = t; } const int g = i >> 2; return 4 * (g + 1) * (2 * g + (i & 3)) + j; };
+      std::vector<int> steps, items;
+      for (int L = maxd; L >= 0; L--) {
+        std::vector<int> piv;
+        for (int k = 0; k < nv; k++) if (depth[k] == L) piv.push_back(k);
+        if (piv.empty()) continue;
+        steps.push_back(0 | ((int)items.size() << 2));
+        for (int k : piv) items.push_back(k | (toff(k, k) << 8));
+        std::vector<std::vector<int>> rounds;
+        std::vector<std::vector<char>> used;
+        for (int k : piv)
+          for (size_t a = 0; a < anc[k].size(); a++)
+            for (size_t b = a; b < anc[k].size(); b++) {
+              const int i = anc[k][a], j = anc[k][b], t = toff(i, j);
+              size_t r = 0;
+              while (r < rounds.size() && used[r][t]) r++;
+              if (r == rounds.size()) { rounds.emplace_back(); used.emplace_back(1024, 0); }
+              used[r][t] = 1;
+              rounds[r].push_back(t | (i << 10) | (j << 16) | (k << 22));
+            }
+        for (auto& rd : rounds) {
+          steps.push_back(1 | ((int)items.size() << 2));
+          items.insert(items.end(), rd.begin(), rd.end());
+        }
+        steps.push_back(2 | ((int)items.size() << 2));
+        for (int k : piv) for (int i : anc[k]) items.push_back(toff(k, i) | (k << 10));
+      }
+      steps.push_back(3 | ((int)items.size() << 2));
+      if ((int)steps.size() > MAXLVSTEP) throw std::string("factorisation program longer than model.cuh's MAXLVSTEP");
+      for (int i = 0; i < MAXLVSTEP; i++) m.lv_steps[i] = i < (int)steps.size() ? steps[i] : steps.back();
+      m.n_lvitems = (int)items.size();
+      for (int i = 0; i < 32; i++) items.push_back(0);
+      PI(m.lv_items, items);
+    }
     std::vector<unsigned char> lca((size_t)nv * nv, 255);
     for (int a = 0; a < nv; a++)
       for (int b = 0; b <= a; b++) {
@@ -705,13 +752,13 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
   return 0;
 }
 
-static int g_extra_smem_solve = 0;   // ADROIT_EXTRA_SMEM_SOLVE: bytes of unused dynamic shared memory added to the solve launches
+static int g_extra_smem[5] = {0, 0, 0, 0, 0};   // ADROIT_EXTRA_SMEM_<phase 0..3>: bytes of unused dynamic shared memory added to that phase's launches (occupancy experiments)
 // dynamic shared memory of a phase kernel: the WPB map slices + 16 bytes per warp for its stage-in mbarrier
 template <typename T, class MAP> constexpr size_t phase_smem() { return MAP::W * map_bytes<T, MAP>() + MAP::W * 16; }
 
 template <typename T, class MAP, typename K>
 int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {
-  size_t smem = phase_smem<T, MAP>() + (phase == 2 ? g_extra_smem_solve : 0);   // (occupancy experiments, tools/gpu_occ_sweep.sh)
+  size_t smem = phase_smem<T, MAP>() + g_extra_smem[phase];   // (occupancy experiments, tools/gpu_occ_sweep.sh)
   int blocks = (a.env1 - a.env0 + MAP::W - 1) / MAP::W;
   if (blocks <= 0) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -743,12 +790,12 @@ int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const D
 }
 
 template <typename T> int configure_kernels() {
-  { const char* e = getenv("ADROIT_EXTRA_SMEM_SOLVE"); g_extra_smem_solve = e ? atoi(e) : 0; }
-  CK(cudaFuncSetAttribute(smooth_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSmooth>()));
-  CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapCollide>()));
-  CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON>>() + g_extra_smem_solve));
-  if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON_S>>() + g_extra_smem_solve));
-  CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapFinish>()));
+  for (int p = 0; p < 4; p++) { char nm[32]; snprintf(nm, sizeof nm, "ADROIT_EXTRA_SMEM_%d", p); const char* e = getenv(nm); g_extra_smem[p] = e ? atoi(e) : 0; }
+  CK(cudaFuncSetAttribute(smooth_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSmooth>() + g_extra_smem[0]));
+  CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapCollide>() + g_extra_smem[1]));
+  CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON>>() + g_extra_smem[2]));
+  if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON_S>>() + g_extra_smem[2]));
+  CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapFinish>() + g_extra_smem[3]));
   CK(cudaFuncSetAttribute(reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapReset>()));
   return 0;
 }
@@ -821,7 +868,7 @@ int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, cons
   memset(&a, 0, sizeof a);
   a.debug = debug;
   int nsub = (s->profile || debug) ? 1 : s->nsub;
-  constexpr int EA = WPB * ADROIT_WPB_SOLVE;        // sub-batch boundaries fall on block boundaries of every phase kernel
+  constexpr int EA = WPB * ADROIT_WPB_SOLVE * (ADROIT_WPB_SMOOTH == WPB ? 1 : ADROIT_WPB_SMOOTH);        // sub-batch boundaries fall on block boundaries of every phase kernel
   int per = ((st.n + nsub - 1) / nsub + EA - 1) / EA * EA;
   if (per < 64 * WPB) { per = (64 * WPB + EA - 1) / EA * EA; }          // never less than 64 blocks per launch
   nsub = (st.n + per - 1) / per;

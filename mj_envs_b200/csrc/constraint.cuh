@@ -675,6 +675,9 @@ template <class CX> PHASE_FN void build_hessian(CX& c) {
 #ifndef ADROIT_STOP_ON_QUADRATIC
 #define ADROIT_STOP_ON_QUADRATIC 1
 #endif
+#ifndef ADROIT_LOCKSTEP_MASK
+#define ADROIT_LOCKSTEP_MASK 15   // which of the four inner barriers of the lockstep iteration are kept (A/B, profiles/R2c_ab_lockstep.txt)
+#endif
 #ifndef ADROIT_LOCKSTEP
 #define ADROIT_LOCKSTEP 2   // 0 = free-running warps, 1 = block barrier per Newton iteration, 2 = block barrier per sub-phase (measured: +10 % hammer)
 #endif
@@ -736,16 +739,16 @@ template <class CX> PHASE_FN void newton(CX& c) {
       if (scale * sqrt(g2) < m.tolerance) act = false;
     }
     if (act && refactor) build_hessian(c);
-    __syncthreads();
+    if (ADROIT_LOCKSTEP_MASK & 1) __syncthreads();
     if (act && refactor) chol_dense(H, c.template V<V_DINV>(), grad, Mv, nv, lane);
-    __syncthreads();
+    if (ADROIT_LOCKSTEP_MASK & 2) __syncthreads();
     if (act) {
       chol_solve(H, c.template V<V_DINV>(), search, nv, lane);
       symv<T, true, true>(M, search, Mv, nv, lane);
       contact_frame_mul(c, search, av);
       __syncwarp();
     }
-    __syncthreads();
+    if (ADROIT_LOCKSTEP_MASK & 4) __syncthreads();
     T alpha = 0;
     if (act) {
       T A0 = 0, B0 = 0;
@@ -775,7 +778,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
       }
       if (alpha == 0) act = false;
     }
-    __syncthreads();
+    if (ADROIT_LOCKSTEP_MASK & 8) __syncthreads();
     if (act) {
       _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) { qacc[j] += alpha * search[j]; Ma[j] += alpha * Mv[j]; }
       _Pragma("unroll 1") for (int r = lane; r < 4 * c.ncon; r += 32) ac[r] += alpha * av[r];
@@ -907,7 +910,7 @@ template <class CX> PHASE_FN void noslip(CX& c) {
       _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
       __syncwarp();
       T* Y = YT + ntan * NVP;
-      symv(Minv, tmp, Y, nv, lane);
+      symv_range(Minv, tmp, Y, nv, lane);
       __syncwarp();
       T dsum = 0;
       _Pragma("unroll 1") for (int i = lane; i < nv; i += 32) dsum += Y[i] * tmp[i];

@@ -244,6 +244,27 @@ template <class CX, int I = 0> DI void stage_out_regions(CX& c) {
     stage_out_regions<CX, I + 1>(c);
   }
 }
+// one staged region written back ahead of the epilogue; returns once the copy engine has read the shared memory, so the
+// region may be overwritten afterwards
+template <int O, int LEN, class CX> DI void store_region_early(CX& c) {
+  using T = typename CX::real;
+  static_assert(CX::template in_smem<O>(), "store_region_early is for staged regions");
+#if ADROIT_BULK_STAGE
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
+  if (c.lane == 0) {
+    bulk_s2g(c.gb + O, c.template S<O>(), LEN * sizeof(T));
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  }
+  __syncwarp();
+#else
+  constexpr int E = 16 / sizeof(T);
+  const T* sp = c.template S<O>();
+  for (int j = c.lane * E; j < LEN; j += 32 * E) *reinterpret_cast<int4*>(c.gb + O + j) = *reinterpret_cast<const int4*>(sp + j);
+  __syncwarp();
+#endif
+}
 // write the R_OUT regions back (call with the warp converged, after the last shared-memory write)
 template <class CX> DI void stage_out(CX& c) {
 #if ADROIT_BULK_STAGE
@@ -471,6 +492,8 @@ template <class CX> PHASE_FN void mass_matrix(CX& c) {
   __syncwarp();
 }
 
+// (scratch: the factor region O_H where the kernel stages one, else O_M -- the smooth kernel runs this before it builds M)
+template <class CX> constexpr int RNE_SCRATCH() { return CX::template in_smem<O_H>() ? O_H : O_M; }
 // recursive Newton-Euler: bias forces (Coriolis + centrifugal + gravity) into V_T1
 template <class CX> PHASE_FN void rne_bias(CX& c) {
   using T = typename CX::real;
@@ -478,8 +501,8 @@ template <class CX> PHASE_FN void rne_bias(CX& c) {
   const T *xpos = c.template S<O_XPOS>(), *xanc = c.template S<O_XANC>(), *xaxis = c.template S<O_XAXIS>(), *qvel = c.template V<V_QVEL>();
   // body velocities / accelerations / forces live in the shared-memory region of the (not yet built) factor O_H: the
   // level loops read what the previous level wrote, and from the context block that was an L2 round trip per level
-  static_assert(18 * NBP <= NTRI, "rne scratch is aliased onto O_H");
-  T *vel = c.template S<O_H>(), *acc = vel + 6 * NBP, *frc = vel + 12 * NBP;
+  static_assert(18 * NBP <= NTRI, "rne scratch is aliased onto the matrix region");
+  T *vel = c.template S<RNE_SCRATCH<CX>()>(), *acc = vel + 6 * NBP, *frc = vel + 12 * NBP;
   if (c.lane == 0) {
     for (int i = 0; i < 6; i++) { vel[i] = 0; frc[i] = 0; }
     acc[0] = acc[1] = acc[2] = 0;
@@ -837,7 +860,42 @@ template <typename T> DI void chol_solve(const T* L, const T* dinv, T* x, int n,
 // only if i is an ancestor dof of k): eliminating leaves first creates no fill-in (Featherstone; MuJoCo's mj_factorM
 // uses the same order).  One step per dof, its (ancestor, ancestor) pair updates spread over the lanes; the schedule
 // ld_start / ld_pair is built on the host.  On return: strict lower part = L, diagonal = D, dinv = 1/D.
-template <typename T> PHASE_FN void ltdl_factor(const DModel<T>& m, T* A, T* dinv, int lane) {
+#ifndef ADROIT_LTDL_LEVEL
+#define ADROIT_LTDL_LEVEL 0   // measured equal to the serial form on B200 (profiles/R2c_ab_lockstep.txt): the chain of ~50 barrier-separated steps is as long as 33 pivots
+#endif
+// Level-scheduled form: the dofs of one depth are eliminated together (the five fingers in parallel, the object's chain
+// alongside), deepest level first: 9-12 levels instead of 30-36 serial pivots.  The program (steps in the kernel
+// parameters, items in the model arena; built on the host, adroit_b200.cu: fill_model) is, per level: reciprocal pivots ->
+// rounds of (ancestor, ancestor) updates with pairwise different targets -> row scaling.  Same products as the serial
+// form below, summed in a fixed (different) order.
+template <typename T> PHASE_FN void ltdl_factor_lv(const DModel<T>& m, T* A, T* dinv, int lane) {
+  const int* items = m.lv_items;
+  int s = 0, w0 = m.lv_steps[0], beg = w0 >> 2;
+  int nxt = items[beg + lane];                         // (the item array is padded by a warp's worth of words)
+#pragma unroll 1
+  while ((w0 & 3) != 3) {
+    const int type = w0 & 3, w1 = m.lv_steps[s + 1], end = w1 >> 2;
+    const int cur = nxt;
+    nxt = items[end + lane];                           // first pass of the next step: off the dependent chain
+#pragma unroll 1
+    for (int p = beg + lane; p < end; p += 32) {
+      const int w = p == beg + lane ? cur : items[p];
+      if (type == 0) {
+        T d = A[w >> 8];
+        d = d > tiny<T>() ? d : tiny<T>();
+        dinv[w & 255] = rcp_t(d);
+      } else if (type == 1) {
+        const int k = (w >> 22) & 63, rk = rowoff(k);
+        A[w & 1023] -= A[rk + ((w >> 10) & 63)] * A[rk + ((w >> 16) & 63)] * dinv[k];
+      } else {
+        A[w & 1023] *= dinv[(w >> 10) & 63];
+      }
+    }
+    __syncwarp();
+    s++; w0 = w1; beg = end;
+  }
+}
+template <typename T> PHASE_FN void ltdl_factor_serial(const DModel<T>& m, T* A, T* dinv, int lane) {
   const int n = m.nv;
   // schedule words (host-built): packed offset of A[i][j] | i << 10 | j << 16.  The first pass of the NEXT pivot's
   // words is fetched while the current pivot is eliminated: no model-table load on the chain of the 33 serial pivots.
@@ -868,6 +926,13 @@ template <typename T> PHASE_FN void ltdl_factor(const DModel<T>& m, T* A, T* din
     if (lane == 0) dinv[k] = inv;
     __syncwarp();
   }
+}
+template <typename T> PHASE_FN void ltdl_factor(const DModel<T>& m, T* A, T* dinv, int lane) {
+#if ADROIT_LTDL_LEVEL
+  ltdl_factor_lv(m, A, dinv, lane);
+#else
+  ltdl_factor_serial(m, A, dinv, lane);
+#endif
 }
 // x <- (L^T D L)^-1 x  (x in shared memory)
 template <typename T> DI void ltdl_solve(const T* L, const T* dinv, T* x, int n, int lane) {
@@ -955,6 +1020,45 @@ template <typename T> PHASE_FN void minv_tree(const DModel<T>& m, T* L, const T*
 // y = A x for a symmetric matrix (lower storage); x, y in shared memory, y != x
 // COMPACT: rolled loops (the solve kernel is instruction-fetch bound: 1.5 KB of code instead of 6 KB)
 // SH: A, x and y are all in shared memory (the solve kernel); otherwise A and x are, y may be anywhere
+// y = A x for an x that is zero outside a (warp-uniform) index range, found by ballot: a contact tangent of the object against
+// the table touches 6 of the 33 dofs, so the row loop runs over 2-3 vector chunks instead of 9 and the transpose loop over 6
+// rows instead of 32.  Same products in the same order as symv for the entries that are not skipped (which are exact zeros).
+template <typename T> SUB_FN void symv_range(const T* A, const T* x, T* y, int n, int lane) {
+  __builtin_assume(__isShared(A));
+  __builtin_assume(__isShared(x));
+  const int i0 = lane, i1 = lane + 32;
+  const T xa = i0 < n ? x[i0] : T(0), xb = i1 < n ? x[i1] : T(0);
+  const unsigned m0 = __ballot_sync(0xffffffffu, xa != T(0)), m1 = __ballot_sync(0xffffffffu, xb != T(0));
+  T y0 = 0, y1 = 0;
+  if (m0 | m1) {
+    const int lo = m0 ? __ffs(m0) - 1 : 32 + __ffs(m1) - 1, hi = m1 ? 63 - __clz(m1) : 31 - __clz(m0);
+    const int k0 = lo & ~3;
+    if (i0 < n) {
+      const T* r = A + rowoff(i0);
+      const int ke = i0 < hi ? i0 : hi;
+      _Pragma("unroll 1") for (int k = k0; k <= ke; k += 4) {
+        Vec4<T> a = ld4(r + k), b = ld4(x + k);
+        y0 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
+      }
+    }
+    if (i1 < n) {
+      const T* r = A + rowoff(i1);
+      const int ke = i1 < hi ? i1 : hi;
+      _Pragma("unroll 1") for (int k = k0; k <= ke; k += 4) {
+        Vec4<T> a = ld4(r + k), b = ld4(x + k);
+        y1 += a.v[0] * b.v[0] + a.v[1] * b.v[1] + a.v[2] * b.v[2] + a.v[3] * b.v[3];
+      }
+    }
+    _Pragma("unroll 2") for (int j = lo > 1 ? lo : 1; j <= hi; j++) {
+      const T* rj = A + rowoff(j);
+      T xj = x[j];
+      if (i0 < j) y0 += rj[i0] * xj;
+      if (j > 32 && i1 < j) y1 += rj[i1] * xj;
+    }
+  }
+  if (i0 < n) y[i0] = y0;
+  if (i1 < n) y[i1] = y1;
+}
 template <typename T, bool COMPACT = false, bool SH = false> SUB_FN void symv(const T* A, const T* x, T* y, int n, int lane) {
   __builtin_assume(__isShared(A));
   __builtin_assume(__isShared(x));
@@ -1031,8 +1135,7 @@ template <class CX> PHASE_FN void smooth_dynamics(CX& c, bool need_minv) {
     qas[j] = f;
     c.template G<G_DBG_BIAS>()[j] = bias[j];
   }
-  T *M = c.template S<O_M>(), *H = c.template S<O_H>();
-  for (int p = c.lane; p < NTRI; p += 32) H[p] = M[p];
+  T* H = c.template S<O_M>();      // factored in place: M itself has already left for the context block (store_region_early)
   __syncwarp();
   ltdl_factor(m, H, c.template V<V_DINV>(), c.lane);
   ltdl_solve(H, c.template V<V_DINV>(), qas, m.nv, c.lane);

@@ -25,6 +25,7 @@ constexpr int MAXSIMPLE = ADROIT_MAXSIMPLE;  // friction-loss + joint-limit + te
 constexpr int NTRI = ADROIT_NTRI;      // lower triangle of a 36x36 matrix, rows padded to multiples of 4 (16-byte aligned rows, see tri())
 constexpr int NPARP = 8;       // per-env model parameters (board_pos | door_body_pos | target quat | obj pos + target pos)
 constexpr int NTF = 24;        // cached task frames (positions the observation / reward read)
+constexpr int MAXLVSTEP = 128; // steps of the level-scheduled factorisation program (Adroit: ~50)
 constexpr int MAXTENDON = 48;  // fixed tendons (Adroit: 44, all limited; at most two joints each)
 #ifndef ADROIT_WPB
 #define ADROIT_WPB 4
@@ -119,6 +120,7 @@ template <typename T> struct DModel {
   const T *tendon_coef, *tendon_range, *tendon_margin, *tendon_invweight0;
   const int* act_dof;
   // tree-sparse factorisation tables (host-built from dof_parent, see fill_model)
+  const int* lv_items;                               // items of the level-scheduled L^T D L program (dynamics.cuh: ltdl_factor), n_lvitems of them
   const int *ld_start, *ld_pair, *wl_pair, *tri_ab;   // [nv+1], [..] tri(i,j)|i<<10|j<<16, [..] k|j<<8, [ntri_real] a|b<<8
   const int *tri_abk;                                // [n_tri] a | b<<8 | lca(a,b)<<16 (255 = none), a >= b
   const int *dof_depth, *anc_tab;                    // [nv] number of proper ancestor dofs, [nv][MAXDEPTH] the chain, nearest first (-1 padded)
@@ -128,6 +130,8 @@ template <typename T> struct DModel {
   const T* render_real;                              // [nrender][19] local pos, local mat, size, rgba (render.cuh)
   int task_int[16];
   // fixed-tendon tables by value: kernel-parameter (constant-bank) reads instead of L2 round trips on the row loops' chain
+  int n_lvitems;
+  int lv_steps[MAXLVSTEP];                           // step s: type (0 pivots, 1 updates, 2 row scaling, 3 end) | first item << 2; it ends where step s+1 starts
   int tdof[2 * MAXTENDON];
   T tcoef[2 * MAXTENDON];
   T par0[NPARP];

@@ -1,3 +1,5 @@
-# solve-kernel throughput against resident blocks per SM (unused dynamic shared memory forces 5 -> 4 -> 3 -> 2 blocks), hammer-v0 x8192
-export WORKLOADS="hammer-v0:8192" STEPS=60 E2E=1
-for x in 0 12000 30000 60000; do echo "== extra smem $x"; ADROIT_EXTRA_SMEM_SOLVE=$x PHASE_TAG=x$x bash tools/gpu_phases.sh; done
+# phase-kernel throughput against resident blocks per SM (unused dynamic shared memory forces fewer resident blocks), hammer-v0 x8192
+# usage: bash tools/gpu_occ_sweep.sh PHASE "BYTES..."    (phase 0 smooth, 1 collide, 2 solve, 3 finish)
+export WORKLOADS="hammer-v0:8192" STEPS=40 E2E=1
+P=${1:-2}
+for x in ${2:-0 12000 30000 60000}; do echo "== phase $P extra smem $x"; env ADROIT_EXTRA_SMEM_$P=$x PHASE_TAG=p${P}x$x bash tools/gpu_phases.sh; done
