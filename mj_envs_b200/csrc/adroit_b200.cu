@@ -60,12 +60,13 @@ struct MapCollide {
   static constexpr int W = WPB;
   static constexpr int NT = 3, NI = 1;
   static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}, Reg{SM_T + G_GPOS, NGP * 3, R_IN}, Reg{SM_T + G_GMAT, NGP * 9, R_IN}};
-  static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV, 0}};
+  static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV / 2, 0}};   // 16-bit entries: 3 blocks/SM stay inside the 32 KB shared-memory carve-out (the kernel lives on L1)
 };
-// The solve kernel comes in two size classes (MC = contact capacity of the shared-memory tables): envs with at most
-// MAXCON_S contacts -- all of them in random play, nearly all under the DAPG policies -- run in the small class, whose
-// shared-memory slice is 11.4 KB per env instead of 13.5 KB: 5 blocks (20 envs) per SM instead of 4 (16).  Each class is
-// its own launch over the same env range; a warp whose env belongs to the other class exits before staging anything.
+// The solve kernel comes in two size classes.  Small (MC = MAXCON_S = 16 contacts, shared-memory contact tables, 11 KB per env):
+// every env in random play, nearly all under the DAPG policies.  Big (MC = MAXCON = 100, the reference's nconmax): the contact
+// tables stay in the context block (L1/L2) -- heavy grasps and pile-ups, rare, and correct up to the reference's capacity
+// instead of dropping contacts beyond 32 as round 1 did.  Each class is its own launch over the same env range; a warp whose
+// env belongs to the other class exits before staging anything.
 #ifndef ADROIT_MAXCON_S
 #define ADROIT_MAXCON_S 16
 #endif
@@ -73,34 +74,53 @@ constexpr int MAXCON_S = ADROIT_MAXCON_S;
 #ifndef ADROIT_WPB_SOLVE
 #define ADROIT_WPB_SOLVE 5    // 4 blocks x 5 envs per SM: measured best of 4 / 5 / 10 / 20 (profiles/R2c_ab_lockstep.txt)
 #endif
+#define SOLVE_COMMON_RT                                                                                                          \
+  VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_QFC, R_ZERO | R_OUT), VR(V_MA, R_ZERO),    \
+      VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_DINV, R_ZERO),                                            \
+      Reg{O_M, NTRI, R_IN},   /* (A/B: reading M from L1/L2 instead costs 30 %) */                                               \
+      Reg{O_H, NTRI, 0}, Reg{O_SD, MAXSIMPLE, 0}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT}
 // WW = warps per block: ADROIT_WPB_SOLVE for the fp32 small class (block-lockstep Newton, constraint.cuh), WPB otherwise
-// (the big class and the fp64 build need 13-26 KB per env: more warps would not fit a block)
 template <int MC, int WW = WPB> struct MapSolveT {
   static constexpr int W = WW;
   static constexpr int NT = 24, NI = 5;
-  static constexpr Reg RT[NT] = {VR(V_WARM, R_IN), VR(V_QFS, R_IN), VR(V_QAS, R_IN), VR(V_QACC, R_ZERO | R_OUT), VR(V_QFC, R_ZERO | R_OUT),
-                                 VR(V_MA, R_ZERO), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_MV, R_ZERO), VR(V_DINV, R_ZERO),
-                                 Reg{O_M, NTRI, R_IN},   // (A/B: reading M from L1/L2 instead costs 30 %)
-                                 Reg{O_H, NTRI, 0},
-                                 Reg{O_SD, MAXSIMPLE, 0}, Reg{O_SAREF, MAXSIMPLE, R_OUT}, Reg{O_SFL, MAXSIMPLE, R_OUT}, Reg{O_SFORCE, MAXSIMPLE, R_OUT},
+  static constexpr Reg RT[NT] = {SOLVE_COMMON_RT,
                                  Reg{O_AC, MC * 4, 0}, Reg{O_AV, MC * 4, 0}, Reg{O_CD, MC, 0}, Reg{O_CMU, MC * 3, R_IN},
                                  Reg{O_CAREFN, MC, 0}, Reg{O_CBT, MC * 3, R_OUT}, Reg{O_EF, MC * 6, R_OUT}, Reg{O_W, MC * 7, 0}};
   static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}, Reg{I_CDIM, MC, R_IN}, Reg{I_CB1, MC, R_IN}, Reg{I_CB2, MC, R_IN},
                                  Reg{I_CMASK, MC, 0}};
 };
+struct MapSolveBig {   // contact tables in the context block
+  static constexpr int W = WPB;
+  static constexpr int NT = 16, NI = 1;
+  static constexpr Reg RT[NT] = {SOLVE_COMMON_RT};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_OUT}};
+};
 template <typename T, int MC> constexpr int solve_w() { return (sizeof(T) == 4 && MC < MAXCON) ? ADROIT_WPB_SOLVE : WPB; }
-template <typename T, int MC> using MapSolveK = MapSolveT<MC, solve_w<T, MC>()>;
-// M^-1 is staged (read-only) for the noslip sweeps; the same shared-memory region then holds the (M + hB) factor
+template <typename T, int MC> struct MapSolvePick { using type = MapSolveT<MC, solve_w<T, MC>()>; };
+template <typename T> struct MapSolvePick<T, MAXCON> { using type = MapSolveBig; };
+template <typename T, int MC> using MapSolveK = typename MapSolvePick<T, MC>::type;
+// M^-1 is staged (read-only) for the noslip sweeps; the same shared-memory region then holds the (M + hB) factor.  Two size
+// classes like the solve kernel: up to MAXCON_M = 32 contacts the contact tables are staged, beyond they stay in the context block.
+#define FINISH_COMMON_RT                                                                                                         \
+  VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),                 \
+      VR(V_QACC, R_IN | R_OUT), VR(V_QFC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_T1, R_ZERO),              \
+      VR(V_DINV, R_ZERO), Reg{SM_T + G_MINV, NTRI, R_IN}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},             \
+      Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}
 struct MapFinish {
   static constexpr int W = WPB;
   static constexpr int NT = 20, NI = 3;
-  static constexpr Reg RT[NT] = {VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),
-                                 VR(V_QACC, R_IN | R_OUT), VR(V_QFC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_T1, R_ZERO),
-                                 VR(V_DINV, R_ZERO), Reg{SM_T + G_MINV, NTRI, R_IN}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},
-                                 Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}, Reg{O_AV, CROWS, 0}, Reg{O_CMU, MAXCON * 3, R_IN},
-                                 Reg{O_CBT, MAXCON * 3, R_IN}, Reg{O_EF, MAXCON * 6, R_IN | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
-  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON, R_IN}, Reg{I_SURV, MAXSURV, 0}};
+  static constexpr Reg RT[NT] = {FINISH_COMMON_RT, Reg{O_AV, MAXCON_M * 4, 0}, Reg{O_CMU, MAXCON_M * 3, R_IN},
+                                 Reg{O_CBT, MAXCON_M * 3, R_IN}, Reg{O_EF, MAXCON_M * 6, R_IN | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON_M, R_IN}, Reg{I_SURV, MAXCON_M * 3, 0}};
 };
+struct MapFinishBig {
+  static constexpr int W = WPB;
+  static constexpr int NT = 16, NI = 1;
+  static constexpr Reg RT[NT] = {FINISH_COMMON_RT, Reg{O_TF, NTF, R_IN | R_OUT}};
+  static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}};
+};
+template <bool BIG> struct MapFinishPick { using type = MapFinish; };
+template <> struct MapFinishPick<true> { using type = MapFinishBig; };
 // the auto-reset of a step (reset_kernel): reset_model + the part of mj_forward the observation reads (kinematics, site frames)
 struct MapReset {
   static constexpr int W = WPB;
@@ -273,11 +293,19 @@ __global__ void __launch_bounds__(MapSolveK<T, MC>::W * 32, (MC < MAXCON && size
 }
 
 // ---------------------------------------------------------------- phase 4: noslip, sensors, Euler, task epilogue
-template <typename T>
+// BIG: envs with more than MAXCON_M contacts (contact tables in the context block, see MapFinishBig); a warp whose env belongs
+// to the other class exits before staging anything
+template <typename T, bool BIG>
 __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                            const __grid_constant__ PArgs a) {
   PDL_WAIT()
-  PHASE_PROLOGUE(MapFinish)
+  {
+    const int env_ = a.env0 + blockIdx.x * WPB + (threadIdx.x >> 5);
+    if (env_ >= a.env1) return;
+    if ((st.ctxi[(size_t)env_ * CTX_I + SM_I + GI_NCON] > MAXCON_M) != BIG) return;
+  }
+  using MapF = typename MapFinishPick<BIG>::type;
+  PHASE_PROLOGUE(MapF)
   const int nv = m.nv;
   c.ncon = c.gi[GI_NCON];
   c.nsimple = c.gi[GI_NSIMPLE];
@@ -304,7 +332,7 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
     }
     for (int i = lane; i < 3 * m.nbody; i += 32) c.template G<G_DBG_XPOS>()[i] = c.template S<O_XPOS>()[i];
     for (int i = lane; i < 4 * m.nbody; i += 32) c.template G<G_DBG_XQUAT>()[i] = c.template S<O_XQUAT>()[i];
-    for (int i = lane; i < 6 * MAXCON; i += 32) c.template G<G_DBG_EF>()[i] = c.template S<O_EF>()[i];
+    for (int i = lane; i < 6 * c.ncon; i += 32) c.template G<G_DBG_EF>()[i] = c.template S<O_EF>()[i];
   }
   __syncwarp();
   T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *warm = c.template V<V_WARM>();
@@ -532,6 +560,7 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
   m.npair = sizes[6]; m.npar = sizes[7]; m.obs_dim = sizes[8]; m.frame_skip = sizes[9]; m.task = sizes[10]; m.horizon = sizes[11];
   if (m.nv > 36 || m.nbody > NBP || m.ngeom > NGP || m.nsite > NSP || m.npar > NPARP || m.nu > NVP)
     throw std::string("model exceeds the compiled capacity of the CUDA kernels");
+  if (m.npair >= 65536) throw std::string("more candidate pairs than the collide kernel's 16-bit pair list can index");
   auto body_parent = B.ints("body_parent"), jntadr = B.ints("body_jntadr"), jntnum = B.ints("body_jntnum");
   auto depth = B.ints("body_depth");
   int nb = m.nbody, maxd = 0;
@@ -795,7 +824,8 @@ template <typename T> int configure_kernels() {
   CK(cudaFuncSetAttribute(collide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapCollide>() + g_extra_smem[1]));
   CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON>>() + g_extra_smem[2]));
   if (MAXCON_S < MAXCON) CK(cudaFuncSetAttribute(solve_kernel<T, MAXCON_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapSolveK<T, MAXCON_S>>() + g_extra_smem[2]));
-  CK(cudaFuncSetAttribute(finish_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapFinish>() + g_extra_smem[3]));
+  CK(cudaFuncSetAttribute(finish_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapFinish>() + g_extra_smem[3]));
+  CK(cudaFuncSetAttribute(finish_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapFinishBig>() + g_extra_smem[3]));
   CK(cudaFuncSetAttribute(reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phase_smem<T, MapReset>()));
   return 0;
 }
@@ -806,7 +836,8 @@ template <typename T> int forward_pass(adroit_sim* s, const DModel<T>& m, const 
   if (launch_phase<T, MapCollide>(s, 1, collide_kernel<T>, m, st, a, stream)) return 1;
   if (MAXCON_S < MAXCON && launch_phase<T, MapSolveK<T, MAXCON_S>>(s, 2, solve_kernel<T, MAXCON_S>, m, st, a, stream)) return 1;
   if (launch_phase<T, MapSolveK<T, MAXCON>>(s, 2, solve_kernel<T, MAXCON>, m, st, a, stream)) return 1;
-  if (launch_phase<T, MapFinish>(s, 3, finish_kernel<T>, m, st, a, stream)) return 1;
+  if (launch_phase<T, MapFinish>(s, 3, finish_kernel<T, false>, m, st, a, stream)) return 1;
+  if (!getenv("ADROIT_NO_BIG_FINISH") && launch_phase<T, MapFinishBig>(s, 3, finish_kernel<T, true>, m, st, a, stream)) return 1;   // (A/B switch)
   return 0;
 }
 

@@ -67,7 +67,7 @@ template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow)
     if (g == var_geom) rb = tmax(rb, sqrt(par[3] * par[3] + par[4] * par[4]));
     return rb;
   };
-  int* surv = c.template I<I_SURV>();
+  unsigned short* surv = reinterpret_cast<unsigned short*>(c.template I<I_SURV>());   // pair indices (< 65536), 16 bits each: MAXSURV / 2 words
   const unsigned lt = (1u << c.lane) - 1u;
   int nsurv = 0;
   for (int base = 0; base < m.npair; base += 32) {
@@ -93,7 +93,7 @@ template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow)
     unsigned mask = __ballot_sync(0xffffffffu, hit);
     if (hit) {
       int p = nsurv + __popc(mask & lt);
-      if (p < MAXSURV) surv[p] = k;
+      if (p < MAXSURV) surv[p] = (unsigned short)k;
     }
     nsurv += __popc(mask);
   }
@@ -267,8 +267,7 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
     for (int i = 0; i < 3; i++) { ax[h][i] = ok ? xaxis[3 * j + i] : T(0); an[h][i] = ok ? xanc[3 * j + i] : T(0); }
     qv[h] = ok ? qvel[j] : T(0);
   }
-  unsigned long long mym1 = 0, mym2 = 0;
-  if (c.lane < c.ncon) { mym1 = m.body_dofmask[c.template I<I_CB1>()[c.lane]]; mym2 = m.body_dofmask[c.template I<I_CB2>()[c.lane]]; }
+  unsigned long long mym1 = 0, mym2 = 0;     // (reloaded at the head of every chunk of 32 contacts)
   T Cn[12];
   if (c.ncon > 0) {
 #pragma unroll
@@ -282,7 +281,11 @@ template <class CX> PHASE_FN void make_constraint(CX& c, unsigned long long* ove
 #pragma unroll
       for (int i = 0; i < 12; i++) Cn[i] = CON[16 * (ci + 1) + 1 + i];
     }
-    const unsigned long long m1 = __shfl_sync(0xffffffffu, mym1, ci), m2 = __shfl_sync(0xffffffffu, mym2, ci);
+    if ((ci & 31) == 0) {                    // warp-uniform
+      mym1 = mym2 = 0;
+      if (ci + c.lane < c.ncon) { mym1 = m.body_dofmask[c.template I<I_CB1>()[ci + c.lane]]; mym2 = m.body_dofmask[c.template I<I_CB2>()[ci + c.lane]]; }
+    }
+    const unsigned long long m1 = __shfl_sync(0xffffffffu, mym1, ci & 31), m2 = __shfl_sync(0xffffffffu, mym2, ci & 31);
     T vsum[4] = {0, 0, 0, 0};
 #pragma unroll
     for (int h = 0; h < 2; h++) {
@@ -356,7 +359,7 @@ template <class CX> SUB_FN void contact_frame_mul(CX c, const typename CX::real*
   using T = typename CX::real;
   assume_spaces(c);
   __builtin_assume(__isShared(x));
-  __builtin_assume(__isShared(out));
+  if constexpr (CX::template in_smem<O_AC>()) __builtin_assume(__isShared(out)); else __builtin_assume(__isGlobal(out));   // O_AC / O_AV
   const T* JR = c.template G<G_JR>();
   const int nv = c.m.nv, lane = c.lane;
   const bool hi = nv > 32 && lane < NVP - 32;
@@ -580,10 +583,38 @@ template <class CX> DI void ls_prepare(CX& c, const typename CX::real* qacc, con
       }
     }
   }
+  if constexpr (CX::MCAP > 32) {   // big class: the edges of contacts 32.. go through a scratch table in the context block
+    T* ls = c.template G<G_LS>();
+    _Pragma("unroll 1") for (int t = 32 * ls_sets<CX>() + c.lane; t < 6 * c.ncon; t += 32) {
+      int ci = t / 6, e = t - 6 * ci, dim = cdim[ci];
+      T x = 0, y = 0, D = 0;
+      if (e < n_edges<T>(dim)) {
+        T sign = 0;
+        int k = 0;
+        x = edge_val(ac + 4 * ci, cmu + 3 * ci, dim, e, sign, k) - (carefn[ci] + sign * cbt[3 * ci + k]);
+        y = edge_val(av + 4 * ci, cmu + 3 * ci, dim, e, sign, k);
+        D = cD[ci];
+      }
+      ls[t] = x; ls[6 * MAXCON + t] = y; ls[12 * MAXCON + t] = D;
+    }
+    __syncwarp();
+  }
+}
+// the same for the edges kept in the context block (big class only): partial sums of (f', f'') before the warp reduction
+template <class CX> DI void ls_eval_tail(CX& c, typename CX::real alpha, typename CX::real& a, typename CX::real& b) {
+  using T = typename CX::real;
+  if constexpr (CX::MCAP > 32) {
+    const T* ls = c.template G<G_LS>();
+    _Pragma("unroll 1") for (int t = 32 * ls_sets<CX>() + c.lane; t < 6 * c.ncon; t += 32) {
+      T D = ls[12 * MAXCON + t], y = ls[6 * MAXCON + t], z = ls[t] + alpha * y;
+      if (D > 0 && z < 0) { a += D * z * y; b += D * y * y; }
+    }
+  }
 }
 // derivative pair (f', f'') of the constraint cost at alpha
-template <typename T, int NE> DI void ls_eval(const LsRows<T, NE>& R, T alpha, T& d1, T& d2) {
+template <class CX, typename T, int NE> DI void ls_eval(CX& c, const LsRows<T, NE>& R, T alpha, T& d1, T& d2) {
   T a = 0, b = 0;
+  ls_eval_tail(c, alpha, a, b);
 #pragma unroll
   for (int q = 0; q < NS_LS; q++) {
     T D = R.Ds[q], y = R.ys[q], z = R.xs[q] + alpha * y;
@@ -758,14 +789,14 @@ template <class CX> PHASE_FN void newton(CX& c) {
       T d1, d2;
       LsRows<T, ls_sets<CX>()> R;
       ls_prepare(c, qacc, search, R);
-      ls_eval(R, T(0), d1, d2);
+      ls_eval(c, R, T(0), d1, d2);
       T f1 = B0 + d1, f2 = A0 + d2;
       if (f1 < 0) {
         const T gtol = (sizeof(T) == 4 ? T(1e-6) : T(1e-13)) * (-f1);
         T lo = 0, hi = -1;  // hi < 0: unbounded
         alpha = -f1 / f2;
         for (int it = 0; it < 40; it++) {
-          ls_eval(R, alpha, d1, d2);
+          ls_eval(c, R, alpha, d1, d2);
           T fa = A0 * alpha + B0 + d1, fb = A0 + d2;
           if (tabs(fa) <= gtol) break;
           if (fa < 0) lo = alpha; else hi = alpha;
@@ -831,7 +862,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     T d1, d2;
     LsRows<T, ls_sets<CX>()> R;
     ls_prepare(c, qacc, search, R);
-    ls_eval(R, T(0), d1, d2);
+    ls_eval(c, R, T(0), d1, d2);
     T f1 = B0 + d1, f2 = A0 + d2;
     T alpha = 0;
     if (f1 < 0) {
@@ -839,7 +870,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
       T lo = 0, hi = -1;  // hi < 0: unbounded
       alpha = -f1 / f2;
       for (int it = 0; it < 40; it++) {
-        ls_eval(R, alpha, d1, d2);
+        ls_eval(c, R, alpha, d1, d2);
         T fa = A0 * alpha + B0 + d1, fb = A0 + d2;
         if (tabs(fa) <= gtol) break;
         if (fa < 0) lo = alpha; else hi = alpha;

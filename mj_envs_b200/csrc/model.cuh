@@ -13,7 +13,11 @@ constexpr int NVP = 36;        // padded dof count (Adroit scenes: 30..36); a mu
 constexpr int NBP = 32;        // bodies (29..31)
 constexpr int NGP = 36;        // collidable geoms (26..33)
 constexpr int NSP = 32;        // sites (28..32)
-constexpr int MAXCON = 32;     // contacts kept per env (overflow is counted, see adroit_overflow)
+#ifndef ADROIT_MAXCON
+#define ADROIT_MAXCON 100
+#endif
+constexpr int MAXCON = ADROIT_MAXCON;    // contacts kept per env = the reference's nconmax (assets/DAPG_assets.xml:4); beyond: counted, adroit_overflow
+constexpr int MAXCON_M = 32;   // contact capacity of the shared-memory tables of the finish kernel's common class (more: tables in the context block)
 constexpr int CROWS = MAXCON * 4;  // contact-frame Jacobian rows: normal, 2 tangents, torsion
 #ifndef ADROIT_MAXSIMPLE
 #define ADROIT_MAXSIMPLE 96
@@ -31,7 +35,8 @@ constexpr int MAXTENDON = 48;  // fixed tendons (Adroit: 44, all limited; at mos
 #define ADROIT_WPB 4
 #endif
 constexpr int WPB = ADROIT_WPB;  // warps (= envs) per block
-constexpr int MAXSURV = 96;    // candidate pairs surviving the bounding-sphere cull
+constexpr int MAXSURV = 192;   // candidate pairs surviving the bounding-sphere cull (shared-memory list of the collide kernel)
+constexpr int NSURVI = (3 * MAXCON > MAXSURV ? 3 * MAXCON + 4 : MAXSURV);    // the I_SURV scratch region of the context block: max(MAXSURV, 3 * MAXCON tangent rows of the noslip pass), 16-byte multiple
 
 enum { T_HAMMER = 0, T_DOOR = 1, T_PEN = 2, T_RELOCATE = 3 };
 enum { J_SLIDE = 2, J_HINGE = 3 };
@@ -77,7 +82,8 @@ constexpr int I_CB1 = I_CDIM + MAXCON;
 constexpr int I_CB2 = I_CB1 + MAXCON;
 constexpr int I_CMASK = I_CB2 + MAXCON;           // active-edge bit mask of every contact (Newton active-set change detection)
 constexpr int I_SURV = I_CMASK + MAXCON;
-constexpr int SM_I = I_SURV + MAXSURV;
+constexpr int SM_I = I_SURV + NSURVI;
+static_assert(NSURVI >= MAXSURV && NSURVI >= 3 * MAXCON && NSURVI % 4 == 0, "I_SURV holds the collide list and the noslip tangent list");
 
 template <typename T> constexpr size_t smem_per_warp() { return SM_T * sizeof(T) + SM_I * sizeof(int); }
 
@@ -94,7 +100,8 @@ constexpr int G_JR = G_CON + MAXCON * 16;        // contact-frame Jacobian, row-
 constexpr int G_LINV = G_JR + CROWS * NVP;       // inverse Cholesky factor of M (packed)
 constexpr int G_MINV = G_LINV + NTRI;            // M^-1 (packed)
 constexpr int G_YT = G_MINV + NTRI;              // M^-1 Jt_k^T for the noslip pass [MAXCON][3][NVP]
-constexpr int G_DBG = G_YT + MAXCON * 3 * NVP;   // debug dump: M packed | qfrc_bias | qfrc_smooth | qacc_smooth | qacc | qfrc_constraint
+constexpr int G_LS = G_YT + MAXCON * 3 * NVP;    // line-search rows of the pyramid edges beyond the register sets (big solve class) [3][6 * MAXCON]: x, y, D
+constexpr int G_DBG = G_LS + 18 * MAXCON;        // debug dump: M packed | qfrc_bias | qfrc_smooth | qacc_smooth | qacc | qfrc_constraint
 constexpr int G_DBG_M = G_DBG, G_DBG_BIAS = G_DBG + NTRI, G_DBG_QFS = G_DBG_BIAS + NVP, G_DBG_QAS = G_DBG_QFS + NVP,
               G_DBG_QACC = G_DBG_QAS + NVP, G_DBG_QFC = G_DBG_QACC + NVP, G_DBG_XPOS = G_DBG_QFC + NVP,
               G_DBG_XQUAT = G_DBG_XPOS + NBP * 3, G_DBG_EF = G_DBG_XQUAT + NBP * 4;

@@ -172,9 +172,10 @@ def test_errors_are_reported_not_swallowed():
 
 @pytest.mark.parametrize("task,scale", [("hammer", 0.35), ("relocate", 0.29)])
 def test_fp64_many_contact_states_cover_both_solve_size_classes(task, scale):
-    """The solve kernel runs in two size classes (<= 16 contacts / up to 32, adroit_b200.cu MapSolveT).  Random play never
-    leaves the small class, so this test builds states with curled, self-colliding fingers: some envs carry 17..32
-    contacts and go through the big class; every env must still match the oracle from identical states."""
+    """The solve kernel runs in two size classes (<= 16 contacts in shared memory / up to the reference's nconmax = 100 with
+    the contact tables in the context block, adroit_b200.cu MapSolveT / MapSolveBig).  Random play never leaves the small
+    class, so this test builds states with curled, self-colliding fingers: some envs carry 17..32 contacts and go through
+    the big class; every env must still match the oracle from identical states."""
     torch, AdroitVecEnv, OracleSim = _mods()
     n = 128
     env = AdroitVecEnv(f"{task}-v0", n, seed=3, fp64=True)
@@ -198,11 +199,58 @@ def test_fp64_many_contact_states_cover_both_solve_size_classes(task, scale):
         gi = np.zeros((n, L["GI_TOTAL"]), dtype=np.int32)
         env.abi.lib.adroit_debug_iscratch(env._h, gi.ctypes.data, None)
         ncon_g = gi[:, 0]
-        assert env.overflow().sum() == 0        # the CUDA path keeps 32 contacts per env; beyond that it only counts
+        assert env.overflow().sum() == 0
         assert np.array_equal(ncon_g, ncon_o)
         big += int((ncon_g > 16).sum())
         gq, gv, _ = env._raw_state()
         nq, nv_, _ = ora.get_state()
         assert _rel(gq, nq).max() < 1e-9 and _rel(gv, nv_).max() < 1e-8, (t, _rel(gq, nq).max(), _rel(gv, nv_).max())
     assert big > 0, "no env exercised the 32-contact size class"
+    env.close()
+
+
+def test_fp64_states_beyond_32_contacts_keep_every_contact_like_the_reference():
+    """The reference model declares nconmax = 100 (assets/DAPG_assets.xml:4); round 1 kept 32 contacts per env and dropped
+    the rest.  A fist pressed into the table and the ball (relocate, arm rolled, fingers curled: states found with the
+    oracle) carries 33..40 contacts: they go through the big classes of the solve AND the finish kernel (contact tables in
+    the context block, line-search rows beyond the register sets in a scratch table), nothing overflows, and the fp64 build
+    matches the oracle -- which keeps 100 contacts -- from identical states."""
+    torch, AdroitVecEnv, OracleSim = _mods()
+    from mj_envs_b200.mjcf import load_compiled
+    task, n = "relocate", 192
+    rng0 = load_compiled(task).A["jnt_range"].reshape(-1, 2)
+    lo, hi = rng0[:, 0], rng0[:, 1]
+    env = AdroitVecEnv(f"{task}-v0", n, seed=5, fp64=True)
+    ora = OracleSim(task, n, seed=5)
+    env.reset(); ora.reset()
+    q, v, p = ora.get_state()
+    rng = np.random.default_rng(2)
+    q = q.copy()
+    for j in range(6):
+        q[:, j] = rng.uniform(lo[j], hi[j], n)
+    q[:, 1] = rng.uniform(0.0, 0.03, n)          # ARTy: hand over the table edge region where palm, fingers and ball meet
+    q[:, 2] = rng.uniform(-0.06, 0.05, n)        # ARTz
+    q[:, 3] = rng.uniform(0.5, 0.62, n)          # ARRx: rolled onto the table
+    frac = rng.uniform(0.3, 1.0, (n, 1))
+    q[:, 6:30] = lo[6:30] + (hi[6:30] - lo[6:30]) * np.clip(frac + rng.uniform(-0.2, 0.2, (n, 24)), 0, 1)
+    ora.set_state(q, np.zeros_like(v), p)
+    L = env.debug_layout()
+    assert L["MAXCON"] == 100
+    beyond = 0
+    for t in range(2):
+        q, v, p = ora.get_state()
+        env._set_raw_state(q, v, p)
+        env.set_warmstart(ora.get_warmstart())
+        a = rng.uniform(-1, 1, (n, env.nu)).astype(np.float32)
+        ora.step(a)
+        env.step(torch.from_numpy(a))
+        _, ncon_o, nefc_o, _ = ora.solver()
+        _, ncon_g, nefc_g, _ = env.solver()
+        assert env.overflow().sum() == 0
+        assert np.array_equal(ncon_g, ncon_o) and np.array_equal(nefc_g, nefc_o)
+        beyond += int((ncon_g > 32).sum())
+        gq, gv, _ = env._raw_state()
+        nq, nv_, _ = ora.get_state()
+        assert _rel(gq, nq).max() < 1e-9 and _rel(gv, nv_).max() < 1e-8, (t, _rel(gq, nq).max(), _rel(gv, nv_).max())
+    assert beyond >= 3, beyond
     env.close()
