@@ -31,13 +31,14 @@ for f in glob.glob(os.path.join(src, f"{tag}_*.ncu-rep")):
         p = l.split()
         if "dram__bytes_read.sum" in l: rd = float(p[1]) * (1e6 if p[2].startswith("M") else 1e9 if p[2].startswith("G") else 1e3 if p[2].startswith("K") else 1)
         if "dram__bytes_write.sum" in l: wr = float(p[1]) * (1e6 if p[2].startswith("M") else 1e9 if p[2].startswith("G") else 1e3 if p[2].startswith("K") else 1)
-    grid = None
+    grid = None; wpb = 4
     for l in out.splitlines():
         if "launch__grid_size" in l: grid = float(l.split()[1])
+        if "launch__block_size" in l: wpb = int(float(l.split()[1])) // 32
     task = name.rsplit("_", 1)[-1]
     if rd is not None and grid and "solve" in name:
-        # DRAM bytes per env of ONE launch of the dominant kernel (4 envs per block); bench.py scales it to its launch size
-        traffic[f"{task}-v0"] = {"dram_bytes_per_env_launch": (rd + wr) / (grid * 4), "kernel": "solve_kernel", "envs_in_captured_launch": int(grid * 4),
+        # DRAM bytes per env of ONE launch of the dominant kernel (block size / 32 envs per block); bench.py scales it to its launch size
+        traffic[f"{task}-v0"] = {"dram_bytes_per_env_launch": (rd + wr) / (grid * wpb), "kernel": "solve_kernel", "envs_in_captured_launch": int(grid * wpb),
                                  "source": f"profiles/{name}.summary.txt"}
     lines.append(f"* `{name}.summary.txt`: `ncu --set full` of one launch ({task}-v0, late episode)")
 for f, tool in ((f"{tag}_hammer_kernels.csv", "ncu_kernels.py"), (f"{tag}_launches.csv", "ncu_launches.py")):

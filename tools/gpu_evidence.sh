@@ -1,7 +1,8 @@
 # One GPU evidence run, parameterised:   gpurun --timeout 3000 -- 'bash tools/gpu_evidence.sh TAG [parts]'
 # parts (default "tests smoke bench ref launches ncu"): tests = pytest -m gpu; smoke; bench = default line (all `also` legs + CPU arm);
 # ref = --impl reference; launches = ncu launch list of the default workload; ncu = one `ncu --set full` capture per phase kernel
-# (hammer-v0 x8192, steady state) + source pages.  Artefacts land in gpurun_out/TAG_*; tools/collect_profiles.py TAG copies
+# (hammer-v0 x8192, steady state, ADROIT_SUBBATCHES=1 so that the captured launch is the whole 8192-env batch: a 512-block sub-batch
+# launch never fills the machine and hides what the kernel is bound by at full occupancy) + source pages.  Artefacts land in gpurun_out/TAG_*; tools/collect_profiles.py TAG copies
 # the judged ones into profiles/.
 TAG=${1:-run}; PARTS=${2:-"tests smoke bench ref launches ncu"}
 has() { case " $PARTS " in *" $1 "*) return 0;; *) return 1;; esac; }
@@ -19,7 +20,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 25000 -
 fi
 if has ncu; then
 for k in ${NCU_KERNELS:-solve finish smooth collide}; do
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:${k}_kernel -s ${NCU_SKIP:-1200} -c 1 -o gpurun_out/${TAG}_${k}_hammer $B > gpurun_out/${TAG}_ncu_${k}.log 2>&1; echo rc=$?
+ADROIT_SUBBATCHES=1 timeout 900 ncu --set full --clock-control none --import-source on -k regex:${k}_kernel -s ${NCU_SKIP:-1200} -c 1 -o gpurun_out/${TAG}_${k}_hammer $B > gpurun_out/${TAG}_ncu_${k}.log 2>&1; echo rc=$?
 timeout 300 ncu -i gpurun_out/${TAG}_${k}_hammer.ncu-rep --page source --csv --print-source cuda,sass > gpurun_out/${TAG}_${k}_hammer.source.csv 2>/dev/null; echo src rc=$?
 done
 fi

@@ -8,12 +8,12 @@ lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(R, "mj_envs_b200", "lib
 L = ctypes.CDLL(lib)
 v = np.zeros(64, dtype=np.int32)
 n = L.adroit_debug_layout(v.ctypes.data_as(ctypes.c_void_p), 64)
-names = ["smooth", "collide", "solve<16>", "solve<32>", "finish", "reset"]
+names = ["smooth", "collide", "solve<16>", "solve<big>", "finish", "reset"]
 smem = dict(zip(names, map(int, v[27:33])))
 regs = {}
 out = subprocess.run(["cuobjdump", "-res-usage", lib], capture_output=True, text=True).stdout
 for fn, rg in re.findall(r"Function (\S+):\s*\n?\s*REG:(\d+)", out):
-    for k, pat in (("smooth", "smooth_kernelIf"), ("collide", "collide_kernelIf"), ("solve<16>", "solve_kernelIfLi16"), ("solve<32>", "solve_kernelIfLi32"),
+    for k, pat in (("smooth", "smooth_kernelIf"), ("collide", "collide_kernelIf"), ("solve<16>", "solve_kernelIfLi16"), ("solve<big>", "solve_kernelIfLi100"),
                    ("finish", "finish_kernelIf"), ("reset", "reset_kernelIf")):
         if pat in fn: regs[k] = int(rg)
 print(f"NVP {v[0]}  NTRI {v[6]}  context block {int(v[33]) * 4 / 1024:.1f} KB + {int(v[34]) * 4 / 1024:.1f} KB ints per env (fp32)")
@@ -23,4 +23,4 @@ for k in names:
     bs = (228 * 1024) // a
     r = regs.get(k, 0)
     br = 65536 // (((r + 7) // 8 * 8) * 128) if r else 0
-    print(f"{k:10s} smem/block {s:6d} B -> {bs:2d} blocks/SM   regs {r:3d} -> {br:2d} blocks/SM   => {min(bs, br) if r else bs} blocks, {4 * (min(bs, br) if r else bs)} warps/SM")
+    print(f"{k:10s} smem/block {s:6d} B -> {bs:2d} blocks/SM   regs {r:3d} -> {br:2d} blocks/SM (at 4 warps per block; the small solve class runs 5)   => {min(bs, br) if r else bs} blocks")

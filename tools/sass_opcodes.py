@@ -14,7 +14,7 @@ for line in txt.splitlines():
     if m: sec = m.group(1); continue
     m = re.match(r"\s*/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\w+\s+)?([A-Z][A-Z0-9_]*)((?:\.[A-Z0-9_]+)*)", line)
     if sec and m: H[sec][m.group(1) + ("" if m.group(1) not in ("UBLKCP", "LDGSTS", "SYNCS", "LD", "ST", "ATOMS", "RED") else m.group(2))] += 1
-want = ["smooth_kernelIf", "collide_kernelIf", "solve_kernelIfLi16", "solve_kernelIfLi32", "finish_kernelIf", "reset_kernelIf"]
+want = ["smooth_kernelIf", "collide_kernelIf", "solve_kernelIfLi16", "solve_kernelIfLi100", "finish_kernelIf", "reset_kernelIf"]
 for s in sorted(H):
     if "--all" not in sys.argv and not any(w in s for w in want): continue
     tot = sum(H[s].values())
