@@ -276,15 +276,17 @@ template <typename T, int MC>
 __global__ void __launch_bounds__(MapSolveK<T, MC>::W * 32, (MC < MAXCON && sizeof(T) == 4) ? ADROIT_SOLVE_BLOCKS : 1)
     solve_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st, const __grid_constant__ PArgs a) {
   PDL_WAIT()
-  if (MAXCON_S < MAXCON) {
+  // class routing: the big class (almost always empty) looks at the contact count BEFORE staging anything; the common class
+  // stages first -- its bulk copies are in flight while the count arrives -- and leaves afterwards if the env is not its own
+  if (MC == MAXCON) {
     const int env_ = a.env0 + blockIdx.x * MapSolveK<T, MC>::W + (threadIdx.x >> 5);
     if (env_ >= a.env1) return;
-    const bool small = st.ctxi[(size_t)env_ * CTX_I + SM_I + GI_NCON] <= MAXCON_S;
-    if (small != (MC < MAXCON)) return;
+    if (st.ctxi[(size_t)env_ * CTX_I + SM_I + GI_NCON] <= MAXCON_S) return;
   }
   using MapK = MapSolveK<T, MC>;
   PHASE_PROLOGUE(MapK)
   c.ncon = c.gi[GI_NCON];
+  if (MC < MAXCON && c.ncon > MAXCON_S) return;
   make_constraint(c, st.overflow);
   newton(c);
   if (lane == 0) c.gi[GI_NSIMPLE] = c.nsimple;
@@ -299,13 +301,14 @@ template <typename T, bool BIG>
 __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                            const __grid_constant__ PArgs a) {
   PDL_WAIT()
-  {
+  if (BIG) {      // (class routing as in solve_kernel)
     const int env_ = a.env0 + blockIdx.x * WPB + (threadIdx.x >> 5);
     if (env_ >= a.env1) return;
-    if ((st.ctxi[(size_t)env_ * CTX_I + SM_I + GI_NCON] > MAXCON_M) != BIG) return;
+    if (st.ctxi[(size_t)env_ * CTX_I + SM_I + GI_NCON] <= MAXCON_M) return;
   }
   using MapF = typename MapFinishPick<BIG>::type;
   PHASE_PROLOGUE(MapF)
+  if (!BIG && c.gi[GI_NCON] > MAXCON_M) return;
   const int nv = m.nv;
   c.ncon = c.gi[GI_NCON];
   c.nsimple = c.gi[GI_NSIMPLE];
@@ -320,6 +323,20 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
     _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) qacc[j] = qas[j] + u[j];
     __syncwarp();
   }
+  // mj_Euler below factors (M + hB) in the shared-memory region that held M^-1: M is fetched from the context block by ONE bulk
+  // copy issued here (second phase of the warp's stage-in mbarrier), in flight while the sensor / task-frame work runs
+  bool m_prefetched = false;
+#if ADROIT_BULK_STAGE
+  if (a.integrate && m.any_damping) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the generic-proxy reads of M^-1 are done
+    __syncwarp();
+    if (lane == 0) {
+      mbar_expect_tx(bar_, (unsigned)(NTRI * sizeof(T)));
+      bulk_g2s(c.template G<G_MINV>(), c.gb + O_M, (unsigned)(NTRI * sizeof(T)), bar_);
+    }
+    m_prefetched = true;
+  }
+#endif
   T touch = touch_sensor(c);
   cache_task_frames(c, touch);
   if (a.debug) {
@@ -337,6 +354,7 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
   __syncwarp();
   T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *warm = c.template V<V_WARM>();
   if (a.integrate) {
+    if (m_prefetched) mbar_wait(bar_, 1);
     // mj_checkAcc: a non-finite acceleration resets the env's data (MuJoCo then re-runs mj_forward on the reset
     // state and integrates it; here the env simply restarts from the reset state on the next substep)
     if (warp_bad(qacc, nv, lane)) {
@@ -349,8 +367,10 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
         T* H = c.template G<G_MINV>();   // the staged copy of M^-1 (noslip is done with it) doubles as the factor buffer
         const T* M = c.template S<O_M>();
         const T *qfs = c.template V<V_QFS>();
-        for (int p = lane; p < NTRI; p += 32) H[p] = M[p];
-        __syncwarp();
+        if (!m_prefetched) {
+          for (int p = lane; p < NTRI; p += 32) H[p] = M[p];
+          __syncwarp();
+        }
         _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) {
           H[tri(j, j)] += h * m.dof_damping[j];
           x[j] = qfs[j] + qfc[j];

@@ -937,18 +937,26 @@ template <class CX> PHASE_FN void noslip(CX& c) {
   for (int ci = 0; ci < c.ncon; ci++) {
     int dim = c.template I<I_CDIM>()[ci];
     for (int k = 0; k + 2 <= dim && k < 3; k++) {
-      const T* Jt = JR + (4 * ci + 1 + k) * NVP;
-      _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) tmp[j] = Jt[j];
+      if (lane == 0) trow[ntan] = 4 * ci + 1 + k;
+      ntan++;
+    }
+  }
+  __syncwarp();
+  {  // the Jacobian row of the NEXT tangent is in flight (L2) while the current one is multiplied
+    T jn0 = 0, jn1 = 0;
+    if (ntan > 0) load_vec(JR + trow[0] * NVP, nv, lane, jn0, jn1);
+    _Pragma("unroll 1") for (int t = 0; t < ntan; t++) {
+      const T j0 = jn0, j1 = jn1;
+      const int row = trow[t], ci = row >> 2, k = (row & 3) - 1;
+      if (t + 1 < ntan) load_vec(JR + trow[t + 1] * NVP, nv, lane, jn0, jn1);
+      store_vec(tmp, nv, lane, j0, j1);
       __syncwarp();
-      T* Y = YT + ntan * NVP;
+      T* Y = YT + t * NVP;
       symv_range(Minv, tmp, Y, nv, lane);
       __syncwarp();
-      T dsum = 0;
-      _Pragma("unroll 1") for (int i = lane; i < nv; i += 32) dsum += Y[i] * tmp[i];
+      T dsum = (lane < nv ? Y[lane] * j0 : T(0)) + (lane + 32 < nv ? Y[lane + 32] * j1 : T(0));
       dsum = warp_sum(dsum);
-      if (lane == 0) { K1[ntan] = 4 * cmu[3 * ci + k] * cmu[3 * ci + k] * dsum; trow[ntan] = 4 * ci + 1 + k; }
-      ntan++;
-      __syncwarp();
+      if (lane == 0) K1[t] = 4 * cmu[3 * ci + k] * cmu[3 * ci + k] * dsum;
     }
   }
   __syncwarp();
