@@ -706,6 +706,14 @@ template <class CX> PHASE_FN void build_hessian(CX& c) {
 #ifndef ADROIT_STOP_ON_QUADRATIC
 #define ADROIT_STOP_ON_QUADRATIC 1
 #endif
+// fp32 stopping rules of the Newton solver (relative line-search gradient tolerance; cost-decrease floor below which an
+// improvement is rounding noise)
+#ifndef ADROIT_F32_LS_GTOL
+#define ADROIT_F32_LS_GTOL 1e-6
+#endif
+#ifndef ADROIT_F32_COST_FLOOR
+#define ADROIT_F32_COST_FLOOR 2e-7   // measured (tools/gpu_fp32_outliers.py): 2e-6 left single-step errors up to 8.7e-5 (hammer) / 4.6e-4 (pen) against
+#endif                               // the fp64 oracle, 2e-7 gives 1.0e-6 / 4.6e-5 -- every agreeing env-step inside the north-star 1e-4 -- for 1 % of throughput
 #ifndef ADROIT_LOCKSTEP_MASK
 #define ADROIT_LOCKSTEP_MASK 15   // which of the four inner barriers of the lockstep iteration are kept (A/B, profiles/R2c_ab_lockstep.txt)
 #endif
@@ -792,7 +800,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
       ls_eval(c, R, T(0), d1, d2);
       T f1 = B0 + d1, f2 = A0 + d2;
       if (f1 < 0) {
-        const T gtol = (sizeof(T) == 4 ? T(1e-6) : T(1e-13)) * (-f1);
+        const T gtol = (sizeof(T) == 4 ? T(ADROIT_F32_LS_GTOL) : T(1e-13)) * (-f1);
         T lo = 0, hi = -1;  // hi < 0: unbounded
         alpha = -f1 / f2;
         for (int it = 0; it < 40; it++) {
@@ -818,7 +826,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
       cost = constraint_update(c, qacc, true) + gauss(qacc, Ma);
       refactor = c.nchanged != 0;
       iters = iter + 1;
-      T floor_ = sizeof(T) == 4 ? T(2e-6) * tabs(cost) : T(0);
+      T floor_ = sizeof(T) == 4 ? T(ADROIT_F32_COST_FLOOR) * tabs(cost) : T(0);
       bool stop = scale * (old - cost) < m.tolerance || (old - cost) < floor_;
 #if ADROIT_STOP_ON_QUADRATIC
       stop = stop || (!refactor && !c.nflipped);
@@ -866,7 +874,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     T f1 = B0 + d1, f2 = A0 + d2;
     T alpha = 0;
     if (f1 < 0) {
-      const T gtol = (sizeof(T) == 4 ? T(1e-6) : T(1e-13)) * (-f1);
+      const T gtol = (sizeof(T) == 4 ? T(ADROIT_F32_LS_GTOL) : T(1e-13)) * (-f1);
       T lo = 0, hi = -1;  // hi < 0: unbounded
       alpha = -f1 / f2;
       for (int it = 0; it < 40; it++) {
@@ -891,7 +899,7 @@ template <class CX> PHASE_FN void newton(CX& c) {
     iters = iter + 1;
     // fp32: an improvement below the rounding noise of the cost itself (~1e-6 relative) cannot be measured; Newton's
     // quadratic convergence makes the step after such an iteration a no-op, so stop there instead of burning a factorisation
-    T floor_ = sizeof(T) == 4 ? T(2e-6) * tabs(cost) : T(0);
+    T floor_ = sizeof(T) == 4 ? T(ADROIT_F32_COST_FLOOR) * tabs(cost) : T(0);
     if (scale * (old - cost) < m.tolerance || (old - cost) < floor_) break;
 #if ADROIT_STOP_ON_QUADRATIC
     // no row / edge changed state along the step: the cost was exactly quadratic on it and the Newton step landed on
