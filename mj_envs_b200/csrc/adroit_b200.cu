@@ -46,9 +46,9 @@ struct PArgs {
 #endif
 struct MapSmooth {
   static constexpr int W = ADROIT_WPB_SMOOTH;   // warps (= envs) per block of the kernel that uses this map
-  static constexpr int NT = 16, NI = 1;
-  static constexpr Reg RT[NT] = {VR(V_CTRL, R_IN | R_OUT), VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_QFS, R_ZERO | R_OUT),
-                                 VR(V_QAS, R_ZERO | R_OUT), VR(V_T1, R_ZERO), VR(V_T2, R_ZERO), VR(V_DINV, R_ZERO),
+  static constexpr int NT = 14, NI = 1;
+  static constexpr Reg RT[NT] = {VR(V_CTRL, R_IN | R_OUT), VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT),
+                                 VR(V_QAS, R_ZERO | R_OUT), VR(V_T1, R_ZERO), VR(V_DINV, R_ZERO),
                                  Reg{O_PAR, NPARP, R_IN | R_OUT}, Reg{O_XPOS, NBP * 3, R_OUT}, Reg{O_XQUAT, NBP * 4, R_OUT},
                                  Reg{O_XMAT, NBP * 9, R_OUT}, Reg{O_XANC, NVP * 3, R_OUT}, Reg{O_XAXIS, NVP * 3, R_OUT},
                                  Reg{O_CRB, NBP * 10, 0}, Reg{O_M, NTRI, 0}};   // M: stored early by the kernel itself, then factored in place
@@ -101,21 +101,23 @@ template <typename T> struct MapSolvePick<T, MAXCON> { using type = MapSolveBig;
 template <typename T, int MC> using MapSolveK = typename MapSolvePick<T, MC>::type;
 // M^-1 is staged (read-only) for the noslip sweeps; the same shared-memory region then holds the (M + hB) factor.  Two size
 // classes like the solve kernel: up to MAXCON_M = 32 contacts the contact tables are staged, beyond they stay in the context block.
+// (shared memory bounds the occupancy: qfrc_smooth / qacc_smooth are read from the context block where needed, and the two
+// scratch vectors of the noslip pass serve again afterwards -- V_GRAD as the solve vector of the Euler step, V_SEARCH as the
+// reciprocal pivots of its factorisation: 7 blocks per SM instead of 6)
 #define FINISH_COMMON_RT                                                                                                         \
-  VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QFS, R_IN), VR(V_QAS, R_IN),                 \
-      VR(V_QACC, R_IN | R_OUT), VR(V_QFC, R_IN | R_OUT), VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), VR(V_T1, R_ZERO),              \
-      VR(V_DINV, R_ZERO), Reg{SM_T + G_MINV, NTRI, R_IN}, Reg{O_SAREF, MAXSIMPLE, R_IN}, Reg{O_SFL, MAXSIMPLE, R_IN},             \
-      Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}
+  VR(V_QPOS, R_IN | R_OUT), VR(V_QVEL, R_IN | R_OUT), VR(V_WARM, R_IN | R_OUT), VR(V_QACC, R_IN | R_OUT), VR(V_QFC, R_IN | R_OUT), \
+      VR(V_GRAD, R_ZERO), VR(V_SEARCH, R_ZERO), Reg{SM_T + G_MINV, NTRI, R_IN}, Reg{O_SAREF, MAXSIMPLE, R_IN},                    \
+      Reg{O_SFL, MAXSIMPLE, R_IN}, Reg{O_SFORCE, MAXSIMPLE, R_IN | R_OUT}
 struct MapFinish {
   static constexpr int W = WPB;
-  static constexpr int NT = 20, NI = 3;
-  static constexpr Reg RT[NT] = {FINISH_COMMON_RT, Reg{O_AV, MAXCON_M * 4, 0}, Reg{O_CMU, MAXCON_M * 3, R_IN},
+  static constexpr int NT = 16, NI = 3;
+  static constexpr Reg RT[NT] = {FINISH_COMMON_RT, Reg{O_AV, MAXCON_M * 3, 0}, Reg{O_CMU, MAXCON_M * 3, R_IN},
                                  Reg{O_CBT, MAXCON_M * 3, R_IN}, Reg{O_EF, MAXCON_M * 6, R_IN | R_OUT}, Reg{O_TF, NTF, R_IN | R_OUT}};
   static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}, Reg{I_CDIM, MAXCON_M, R_IN}, Reg{I_SURV, MAXCON_M * 3, 0}};
 };
 struct MapFinishBig {
   static constexpr int W = WPB;
-  static constexpr int NT = 16, NI = 1;
+  static constexpr int NT = 12, NI = 1;
   static constexpr Reg RT[NT] = {FINISH_COMMON_RT, Reg{O_TF, NTF, R_IN | R_OUT}};
   static constexpr Reg RI[NI] = {Reg{I_SINFO, MAXSIMPLE, R_IN}};
 };
@@ -316,7 +318,7 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
   if (m.noslip_iterations > 0) {
     noslip(c);
     constraint_force(c);
-    T* u = c.template V<V_T1>();
+    T* u = c.template V<V_GRAD>();   // (the noslip pass is done with its copy)
     symv(c.template G<G_MINV>(), qfc, u, nv, lane);
     __syncwarp();
     const T* qas = c.template V<V_QAS>();
@@ -361,7 +363,7 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
       zero_state(c);
     } else {
       // mj_Euler: semi-implicit with implicit joint damping, (M + h*diag(damping)) keeps the tree sparsity of M
-      T* x = c.template V<V_T1>();
+      T* x = c.template V<V_GRAD>();
       const T h = m.timestep;
       if (m.any_damping) {
         T* H = c.template G<G_MINV>();   // the staged copy of M^-1 (noslip is done with it) doubles as the factor buffer
@@ -376,8 +378,8 @@ __global__ void __launch_bounds__(WPB * 32) finish_kernel(const __grid_constant_
           x[j] = qfs[j] + qfc[j];
         }
         __syncwarp();
-        ltdl_factor(m, H, c.template V<V_DINV>(), lane);
-        ltdl_solve(H, c.template V<V_DINV>(), x, nv, lane);
+        ltdl_factor(m, H, c.template V<V_SEARCH>(), lane);
+        ltdl_solve(H, c.template V<V_SEARCH>(), x, nv, lane);
       } else {
         _Pragma("unroll 1") for (int j = lane; j < nv; j += 32) x[j] = qacc[j];
         __syncwarp();

@@ -1071,7 +1071,16 @@ template <class CX> PHASE_FN void noslip(CX& c) {
 template <class CX> PHASE_FN void constraint_force(CX& c) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
-  T *qfc = c.template V<V_QFC>(), *F = c.template S<O_AV>();
+  T* qfc = c.template V<V_QFC>();
+  // frame-force scratch [ncon][4]: the O_AV region -- unless the kernel stages it too small for that (the finish kernel keeps
+  // only the noslip pass's K1[3 * MAXCON_M] there); then the staged, by now dead, saref | floss rows serve (adjacent, 2 * MAXSIMPLE)
+  T* F;
+  if constexpr (map_rlen<typename CX::MAP>(O_AV) > 0 && map_rlen<typename CX::MAP>(O_AV) < 4 * MAXCON_M) {
+    static_assert(CX::template in_smem<O_SAREF>() && CX::template in_smem<O_SFL>() && O_SFL == O_SAREF + MAXSIMPLE && 2 * MAXSIMPLE >= 4 * MAXCON_M, "");
+    F = c.template S<O_SAREF>();
+  } else {
+    F = c.template S<O_AV>();
+  }
   const int* sinfo = c.template I<I_SINFO>();
   const T *sforce = c.template S<O_SFORCE>(), *ef = c.template S<O_EF>(), *cmu = c.template S<O_CMU>();
   _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) qfc[j] = 0;

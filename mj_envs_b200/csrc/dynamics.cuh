@@ -1119,18 +1119,21 @@ template <typename T> DI T sym_get(const T* A, int i, int j) { return i >= j ? A
 template <class CX> PHASE_FN void smooth_dynamics(CX& c, bool need_minv) {
   using T = typename CX::real;
   const DModel<T>& m = c.m;
-  const T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *bias = c.template V<V_T1>(), *ctrl = c.template V<V_CTRL>();
-  T *qfs = c.template V<V_QFS>(), *qas = c.template V<V_QAS>(), *act = c.template V<V_T2>();
-  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) act[j] = 0;
+  const T *qpos = c.template V<V_QPOS>(), *qvel = c.template V<V_QVEL>(), *ctrl = c.template V<V_CTRL>();
+  // shared memory is what bounds this kernel's occupancy (7 blocks/SM with the map as it is): the actuator forces are
+  // gathered in the qacc_smooth vector itself, qfrc_smooth goes straight to the context block (V_QFS is not staged here),
+  // and the bias vector's slot doubles as the int scratch of minv_tree once the forces are formed
+  T *bias = c.template V<V_T1>(), *qfs = c.template V<V_QFS>(), *qas = c.template V<V_QAS>();
+  _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) qas[j] = 0;
   __syncwarp();
   _Pragma("unroll 1") for (int u = c.lane; u < m.nu; u += 32) {
     T cu = tclamp(ctrl[u], m.act_ctrlrange[2 * u], m.act_ctrlrange[2 * u + 1]);
     int j = m.act_dof[u];
-    act[j] = m.act_gain[u] * cu + m.act_bias[3 * u] + m.act_bias[3 * u + 1] * qpos[j] + m.act_bias[3 * u + 2] * qvel[j];
+    qas[j] = m.act_gain[u] * cu + m.act_bias[3 * u] + m.act_bias[3 * u + 1] * qpos[j] + m.act_bias[3 * u + 2] * qvel[j];
   }
   __syncwarp();
   _Pragma("unroll 1") for (int j = c.lane; j < m.nv; j += 32) {
-    T f = -m.dof_damping[j] * qvel[j] - bias[j] + act[j];
+    T f = -m.dof_damping[j] * qvel[j] - bias[j] + qas[j];
     qfs[j] = f;
     qas[j] = f;
     c.template G<G_DBG_BIAS>()[j] = bias[j];
@@ -1139,7 +1142,7 @@ template <class CX> PHASE_FN void smooth_dynamics(CX& c, bool need_minv) {
   __syncwarp();
   ltdl_factor(m, H, c.template V<V_DINV>(), c.lane);
   ltdl_solve(H, c.template V<V_DINV>(), qas, m.nv, c.lane);
-  if (need_minv) minv_tree(m, H, c.template V<V_DINV>(), reinterpret_cast<int*>(act), c.template G<G_MINV>(), c.lane);   // act (V_T2): free by now
+  if (need_minv) minv_tree(m, H, c.template V<V_DINV>(), reinterpret_cast<int*>(bias), c.template G<G_MINV>(), c.lane);   // bias (V_T1): free by now
 }
 
 }  // namespace adroit
