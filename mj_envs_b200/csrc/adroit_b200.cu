@@ -20,7 +20,7 @@ namespace adroit {
 
 enum { MODE_STEP = 0, MODE_RESET = 1, MODE_FORWARD = 2 };
 #ifndef ADROIT_DEFAULT_SUBBATCHES
-#define ADROIT_DEFAULT_SUBBATCHES 4
+#define ADROIT_DEFAULT_SUBBATCHES 3   // measured (round 2, tools/gpu_subbatch_sweep.sh): 3 >= 4 at 8192 and 16384 envs, mostly in the end-to-end number
 #endif
 
 struct PArgs {
