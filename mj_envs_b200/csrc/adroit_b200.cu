@@ -58,6 +58,7 @@ struct MapSmooth {
 // every test starts with two position reads; the kernel is register-bound (2 blocks/SM), shared memory is free
 struct MapCollide {
   static constexpr int W = WPB;
+  static constexpr int EXTRA = WPB * 16 + WPB * MPRQ * 2;   // per warp: queue length (16-byte slot) + MPRQ 16-bit pair indices
   static constexpr int NT = 3, NI = 1;
   static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}, Reg{SM_T + G_GPOS, NGP * 3, R_IN}, Reg{SM_T + G_GMAT, NGP * 9, R_IN}};
   static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV / 2, 0}};   // 16-bit entries: 3 blocks/SM stay inside the 32 KB shared-memory carve-out (the kernel lives on L1)
@@ -244,9 +245,48 @@ template <typename T>
 __global__ void __launch_bounds__(WPB * 32, ADROIT_COLLIDE_BLOCKS) collide_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                             const __grid_constant__ PArgs a) {
   PDL_WAIT()
-  PHASE_PROLOGUE(MapCollide)
-  collision(c, st.overflow);
-  if (lane == 0) c.gi[GI_NCON] = c.ncon;
+  // (no early return in this kernel: every warp reaches the two block barriers around the pooled MPR pass)
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using MAP = MapCollide;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int env = a.env0 + blockIdx.x * MAP::W + warp;
+  const bool alive = env < a.env1 && !(a.mask && !a.mask[env]);
+  const int envc = alive ? env : a.env0;             // (pointer arithmetic only for a warp without an env)
+  T* sm_ = reinterpret_cast<T*>(smem_raw) + (size_t)warp * map_st<MAP>();
+  int* smi_ = reinterpret_cast<int*>(smem_raw + (size_t)MAP::W * map_st<MAP>() * sizeof(T)) + warp * map_si<MAP>();
+  unsigned char* tail = smem_raw + (size_t)MAP::W * map_bytes<T, MAP>();
+  unsigned long long* bar_ = reinterpret_cast<unsigned long long*>(tail) + 2 * warp;
+  int* qn = reinterpret_cast<int*>(tail + MAP::W * 16);                                       // [W] (stride 4 ints)
+  unsigned short* qk = reinterpret_cast<unsigned short*>(tail + MAP::W * 32);                 // [W][MPRQ]
+  Ctx<T, MAP> c(m, sm_, smi_, st.ctx + (size_t)envc * CTX_T, st.ctxi + (size_t)envc * CTX_I, lane);
+  if (lane == 0) qn[4 * warp] = 0;
+  int nsurv = 0;
+  if (alive) {
+    stage_in(c, bar_);
+    __syncwarp();
+    nsurv = collision_broad(c, st.overflow, qk + warp * MPRQ, qn + 4 * warp);
+  }
+  __syncthreads();
+  {  // pooled MPR: thread e of the block takes the e-th queued pair of the block's envs
+    int off[MAP::W + 1];
+    off[0] = 0;
+#pragma unroll
+    for (int w = 0; w < MAP::W; w++) off[w + 1] = off[w] + qn[4 * w];
+    for (int e = threadIdx.x; e < off[MAP::W]; e += MAP::W * 32) {
+      int w = 0;
+#pragma unroll
+      for (int q = 1; q < MAP::W; q++) w += e >= off[q];
+      const int j = e - off[w];
+      const T* smw = reinterpret_cast<const T*>(smem_raw) + (size_t)w * map_st<MAP>();
+      T* gbw = st.ctx + (size_t)(a.env0 + blockIdx.x * MAP::W + w) * CTX_T;
+      collision_mpr_entry<Ctx<T, MAP>>(m, smw + map_soff<MAP>(SM_T + G_GPOS), smw + map_soff<MAP>(SM_T + G_GMAT), gbw, qk[w * MPRQ + j], j);
+    }
+  }
+  __syncthreads();
+  if (alive) {
+    collision_narrow(c, nsurv, st.overflow);
+    if (lane == 0) c.gi[GI_NCON] = c.ncon;
+  }
 }
 
 // ---------------------------------------------------------------- auto-reset inside env.step()
@@ -805,7 +845,10 @@ template <typename T> int alloc_state(adroit_sim* s, DState<T>& st) {
 
 static int g_extra_smem[5] = {0, 0, 0, 0, 0};   // ADROIT_EXTRA_SMEM_<phase 0..3>: bytes of unused dynamic shared memory added to that phase's launches (occupancy experiments)
 // dynamic shared memory of a phase kernel: the WPB map slices + 16 bytes per warp for its stage-in mbarrier
-template <typename T, class MAP> constexpr size_t phase_smem() { return MAP::W * map_bytes<T, MAP>() + MAP::W * 16; }
+// (+ MAP::EXTRA bytes per block where the map declares them: the collide kernel's MPR queues)
+template <class MAP, class = void> struct map_extra { static constexpr size_t value = 0; };
+template <class MAP> struct map_extra<MAP, decltype((void)MAP::EXTRA)> { static constexpr size_t value = MAP::EXTRA; };
+template <typename T, class MAP> constexpr size_t phase_smem() { return MAP::W * map_bytes<T, MAP>() + MAP::W * 16 + map_extra<MAP>::value; }
 
 template <typename T, class MAP, typename K>
 int launch_phase(adroit_sim* s, int phase, K kernel, const DModel<T>& m, const DState<T>& st, const PArgs& a, cudaStream_t stream) {

@@ -53,31 +53,60 @@ template <typename T> DI T shape_lower_bound(int type, const T* R, const T* size
 }
 
 // ---------------------------------------------------------------- collision over the static candidate list
-template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow) {
+// Three steps (collide_kernel, adroit_b200.cu):
+//   1. collision_broad  (per warp = env): bounding-sphere + shape-aware cull of the static candidate list, survivors
+//      compacted into a 16-bit list (lane = pair, ballot); the survivors whose type pair goes to MPR (anything with a
+//      cylinder but plane-cylinder) are also pushed, in survivor order, into the warp's queue in shared memory;
+//   2. collision_mpr_pool (whole block): the queues of the block's envs are worked off together, one lane per queued pair --
+//      MPR (fp64 portal refinement, ~40 % of the kernel) then runs once per block in full lanes instead of once per env in
+//      one or two lanes; results go to the env's G_MPRRES slots;
+//   3. collision_narrow (per warp): the analytic routines, lane = survivor; queued pairs pick up their MPR result; ordered
+//      compaction keeps MuJoCo's contact order (candidate-list order).
+template <class CX> struct CollideGeom {
   using T = typename CX::real;
-  const DModel<T>& m = c.m;
-  const T *gpos = c.template G<G_GPOS>(), *gmat = c.template G<G_GMAT>();
+  const DModel<T>& m;
+  const T *gpos, *gmat, *par;
+  int var_geom;
   // hammer "size" variation (hammer_v0.py:123-125): geom_size of the head is a per-env parameter; geom_rbound stays stale
   // as in MuJoCo (the model is not recompiled), except in this file's own extra culls, which must stay conservative
-  const int var_geom = m.task_int[8] == VAR_SIZE ? m.task_int[10] : -1;
-  const T *par = c.template S<O_PAR>();
-  auto gsize = [&](int g, int k) -> T { return (g == var_geom && k < 2) ? par[3 + k] : m.geom_size[3 * g + k]; };
-  auto rb_safe = [&](int g) -> T {
+  __device__ CollideGeom(const DModel<T>& mm, const T* gp, const T* gm, const T* pr)
+      : m(mm), gpos(gp), gmat(gm), par(pr), var_geom(mm.task_int[8] == VAR_SIZE ? mm.task_int[10] : -1) {}
+  DI T gsize(int g, int k) const { return (g == var_geom && k < 2) ? par[3 + k] : m.geom_size[3 * g + k]; }
+  DI T rb_safe(int g) const {
     T rb = m.geom_rbound[g];
     if (g == var_geom) rb = tmax(rb, sqrt(par[3] * par[3] + par[4] * par[4]));
     return rb;
-  };
+  }
+  // pair k with geom1 translated to the origin
+  DI void pair(int k, int& g1, int& g2, M3<T>& R1, M3<T>& R2, V3<T>& origin, V3<T>& p2, V3<T>& s1, V3<T>& s2) const {
+    g1 = m.pair_geom[2 * k];
+    g2 = m.pair_geom[2 * k + 1];
+    for (int e = 0; e < 9; e++) { R1.m[e] = gmat[9 * g1 + e]; R2.m[e] = gmat[9 * g2 + e]; }
+    origin = mk<T>(gpos[3 * g1], gpos[3 * g1 + 1], gpos[3 * g1 + 2]);
+    p2 = mk<T>(gpos[3 * g2], gpos[3 * g2 + 1], gpos[3 * g2 + 2]) - origin;
+    s1 = mk<T>(gsize(g1, 0), gsize(g1, 1), gsize(g1, 2));
+    s2 = mk<T>(gsize(g2, 0), gsize(g2, 1), gsize(g2, 2));
+  }
+};
+
+// returns the number of survivors (list in I_SURV); qk / qn: this warp's MPR queue (pair indices, count)
+template <class CX> PHASE_FN int collision_broad(CX& c, unsigned long long* overflow, unsigned short* qk, int* qn) {
+  using T = typename CX::real;
+  const DModel<T>& m = c.m;
+  const CollideGeom<CX> G(m, c.template G<G_GPOS>(), c.template G<G_GMAT>(), c.template S<O_PAR>());
+  const T *gpos = G.gpos, *gmat = G.gmat;
   unsigned short* surv = reinterpret_cast<unsigned short*>(c.template I<I_SURV>());   // pair indices (< 65536), 16 bits each: MAXSURV / 2 words
   const unsigned lt = (1u << c.lane) - 1u;
-  int nsurv = 0;
+  int nsurv = 0, nmpr = 0;
   for (int base = 0; base < m.npair; base += 32) {
     int k = base + c.lane;
-    bool hit = false;
+    bool hit = false, mpr = false;
     if (k < m.npair) {
       int g1 = m.pair_geom[2 * k], g2 = m.pair_geom[2 * k + 1];
       T margin = m.pair_margin[k];
       T dx = gpos[3 * g2] - gpos[3 * g1], dy = gpos[3 * g2 + 1] - gpos[3 * g1 + 1], dz = gpos[3 * g2 + 2] - gpos[3 * g1 + 2];
-      if (m.geom_type[g1] == G_PLANE) {
+      const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
+      if (t1 == G_PLANE) {
         const T* R = gmat + 9 * g1;
         hit = !(dx * R[2] + dy * R[5] + dz * R[8] > m.geom_rbound[g2] + margin);
       } else {
@@ -85,42 +114,82 @@ template <class CX> PHASE_FN void collision(CX& c, unsigned long long* overflow)
         hit = !(dx * dx + dy * dy + dz * dz > bound * bound);
         // second, tighter (still conservative) test: the other geom's bounding sphere against this geom's own shape
         // (large boxes -- table, wall, door -- have bounding spheres that swallow the whole hand)
-        T z1[3] = {gsize(g1, 0), gsize(g1, 1), gsize(g1, 2)}, z2[3] = {gsize(g2, 0), gsize(g2, 1), gsize(g2, 2)};
-        if (hit) hit = !(shape_lower_bound(m.geom_type[g1], gmat + 9 * g1, z1, dx, dy, dz) > rb_safe(g2) + margin);
-        if (hit) hit = !(shape_lower_bound(m.geom_type[g2], gmat + 9 * g2, z2, -dx, -dy, -dz) > rb_safe(g1) + margin);
+        T z1[3] = {G.gsize(g1, 0), G.gsize(g1, 1), G.gsize(g1, 2)}, z2[3] = {G.gsize(g2, 0), G.gsize(g2, 1), G.gsize(g2, 2)};
+        if (hit) hit = !(shape_lower_bound(t1, gmat + 9 * g1, z1, dx, dy, dz) > G.rb_safe(g2) + margin);
+        if (hit) hit = !(shape_lower_bound(t2, gmat + 9 * g2, z2, -dx, -dy, -dz) > G.rb_safe(g1) + margin);
       }
+      mpr = hit && is_mpr_pair(t1, t2);
     }
     unsigned mask = __ballot_sync(0xffffffffu, hit);
-    if (hit) {
-      int p = nsurv + __popc(mask & lt);
-      if (p < MAXSURV) surv[p] = (unsigned short)k;
-    }
+    int p = nsurv + __popc(mask & lt);
+    if (hit && p < MAXSURV) surv[p] = (unsigned short)k;
+    // (a survivor beyond MAXSURV is dropped and counted below; it is not queued either)
+    unsigned mm = __ballot_sync(0xffffffffu, mpr && p < MAXSURV);
+    int j = nmpr + __popc(mm & lt);
+    if (mpr && p < MAXSURV && j < MPRQ) qk[j] = (unsigned short)k;
     nsurv += __popc(mask);
+    nmpr += __popc(mm);
   }
   if (nsurv > MAXSURV) {
     if (c.lane == 0) atomicAdd(overflow, (unsigned long long)(nsurv - MAXSURV));
     nsurv = MAXSURV;
   }
+  if (c.lane == 0) *qn = nmpr < MPRQ ? nmpr : MPRQ;
   __syncwarp();
-  int ncon = 0;
+  return nsurv;
+}
+
+// one queued MPR pair (all threads of the block call this with their own entry): env_gb = context block of the pair's env
+template <class CX> DI void collision_mpr_entry(const DModel<typename CX::real>& m, const typename CX::real* gpos, const typename CX::real* gmat,
+                                                typename CX::real* env_gb, int k, int slot) {
+  using T = typename CX::real;
+  const CollideGeom<CX> G(m, gpos, gmat, env_gb + O_PAR);
+  int g1, g2;
+  M3<T> R1, R2;
+  V3<T> origin, p2, s1, s2;
+  G.pair(k, g1, g2, R1, R2, origin, p2, s1, s2);
+  T dist = 0;
+  V3<T> pos = mk<T>(0, 0, 0), nrm = mk<T>(0, 0, 0);
+  const bool hit = mpr_contact(m.pair_margin[k], m.geom_type[g1], mk<T>(0, 0, 0), R1, s1, m.geom_type[g2], p2, R2, s2, m.mpr_iterations,
+                               m.mpr_tolerance, dist, pos, nrm);
+  T* R = env_gb + SM_T + G_MPRRES + 8 * slot;
+  R[0] = hit ? T(1) : T(0);
+  R[1] = dist; R[2] = pos.x; R[3] = pos.y; R[4] = pos.z; R[5] = nrm.x; R[6] = nrm.y; R[7] = nrm.z;
+}
+
+template <class CX> PHASE_FN void collision_narrow(CX& c, int nsurv, unsigned long long* overflow) {
+  using T = typename CX::real;
+  const DModel<T>& m = c.m;
+  const CollideGeom<CX> G(m, c.template G<G_GPOS>(), c.template G<G_GMAT>(), c.template S<O_PAR>());
+  const unsigned short* surv = reinterpret_cast<const unsigned short*>(c.template I<I_SURV>());
+  const T* mres = c.template G<G_MPRRES>();
+  const unsigned lt = (1u << c.lane) - 1u;
+  int ncon = 0, nmpr = 0;
   T* cmu = c.template S<O_CMU>();
   for (int base = 0; base < nsurv; base += 32) {
     ConOut<T> out;
     out.n = 0;
     int i = base + c.lane, k = -1, g1 = 0, g2 = 0;
     V3<T> origin = mk<T>(0, 0, 0);
+    bool mpr = false;
     if (i < nsurv) {
       k = surv[i];
-      g1 = m.pair_geom[2 * k];
-      g2 = m.pair_geom[2 * k + 1];
+      mpr = is_mpr_pair(m.geom_type[m.pair_geom[2 * k]], m.geom_type[m.pair_geom[2 * k + 1]]);
+    }
+    const unsigned mm = __ballot_sync(0xffffffffu, mpr);
+    const int j = nmpr + __popc(mm & lt);       // this survivor's place in the warp's MPR queue (same order as collision_broad)
+    nmpr += __popc(mm);
+    if (i < nsurv) {
       M3<T> R1, R2;
-      for (int e = 0; e < 9; e++) { R1.m[e] = gmat[9 * g1 + e]; R2.m[e] = gmat[9 * g2 + e]; }
-      origin = mk<T>(gpos[3 * g1], gpos[3 * g1 + 1], gpos[3 * g1 + 2]);
-      V3<T> p2 = mk<T>(gpos[3 * g2], gpos[3 * g2 + 1], gpos[3 * g2 + 2]) - origin;
-      V3<T> s1 = mk<T>(gsize(g1, 0), gsize(g1, 1), gsize(g1, 2));
-      V3<T> s2 = mk<T>(gsize(g2, 0), gsize(g2, 1), gsize(g2, 2));
-      collide_pair(out, m.pair_margin[k], m.geom_type[g1], mk<T>(0, 0, 0), R1, s1, m.geom_type[g2], p2, R2, s2,
-                   m.mpr_iterations, m.mpr_tolerance);
+      V3<T> p2, s1, s2;
+      G.pair(k, g1, g2, R1, R2, origin, p2, s1, s2);
+      if (mpr && j < MPRQ) {                    // computed by the pooled pass
+        const T* R = mres + 8 * j;
+        if (R[0] != T(0)) out.add(R[1], mk<T>(R[2], R[3], R[4]), mk<T>(R[5], R[6], R[7]), m.pair_margin[k]);
+      } else {
+        collide_pair(out, m.pair_margin[k], m.geom_type[g1], mk<T>(0, 0, 0), R1, s1, m.geom_type[g2], p2, R2, s2,
+                     m.mpr_iterations, m.mpr_tolerance);
+      }
     }
     // ordered compaction: contacts keep candidate-list order (the noslip sweep order depends on it)
     int cnt = out.n, incl = cnt;

@@ -369,18 +369,38 @@ __device__ __noinline__ bool mpr_penetration(const MprObj<T>& o1, const MprObj<T
 // the portal that survives is decided by differences of ~1e-6-scale support values, and in fp32 the surviving portal --
 // hence the contact normal -- flips (measured on B200: every fp32 single-step error above 1e-3 in pen-v0 was an MPR
 // normal, tools/gpu_worst.py).  B200 runs fp64 at half the fp32 rate and MPR pairs are few after the broadphase.
+// the MPR contact of one pair: false = no contact found; otherwise dist / pos / nrm as the narrow phase reports them
 template <typename T>
-DI void c_mpr(ConOut<T>& o, T margin, int t1, V3<T> p1, const M3<T>& R1, V3<T> s1, int t2, V3<T> p2, const M3<T>& R2, V3<T> s2,
-              int max_iter, T tol) {
+DI bool mpr_contact(T margin, int t1, V3<T> p1, const M3<T>& R1, V3<T> s1, int t2, V3<T> p2, const M3<T>& R2, V3<T> s2, int max_iter, T tol,
+                    T& dist, V3<T>& cpos, V3<T>& cnrm) {
   MprObj<double> o1, o2;
   o1.type = t1; o1.pos = mk<double>(p1.x, p1.y, p1.z); o1.size = mk<double>(s1.x, s1.y, s1.z); o1.margin = margin;
   o2.type = t2; o2.pos = mk<double>(p2.x, p2.y, p2.z); o2.size = mk<double>(s2.x, s2.y, s2.z); o2.margin = margin;
   for (int e = 0; e < 9; e++) { o1.R.m[e] = R1.m[e]; o2.R.m[e] = R2.m[e]; }
   double depth;
   V3<double> dir, pos;
-  if (!mpr_penetration<double>(o1, o2, max_iter, (double)tol, depth, dir, pos)) return;
-  if (dot(dir, dir) < 0.5) return;
-  o.add(margin - (T)depth, mk<T>((T)pos.x, (T)pos.y, (T)pos.z), mk<T>((T)dir.x, (T)dir.y, (T)dir.z), margin);
+  if (!mpr_penetration<double>(o1, o2, max_iter, (double)tol, depth, dir, pos)) return false;
+  if (dot(dir, dir) < 0.5) return false;
+  dist = margin - (T)depth;
+  cpos = mk<T>((T)pos.x, (T)pos.y, (T)pos.z);
+  cnrm = mk<T>((T)dir.x, (T)dir.y, (T)dir.z);
+  return true;
+}
+template <typename T>
+DI void c_mpr(ConOut<T>& o, T margin, int t1, V3<T> p1, const M3<T>& R1, V3<T> s1, int t2, V3<T> p2, const M3<T>& R2, V3<T> s2,
+              int max_iter, T tol) {
+  T dist;
+  V3<T> pos, nrm;
+  if (mpr_contact(margin, t1, p1, R1, s1, t2, p2, R2, s2, max_iter, tol, dist, pos, nrm)) o.add(dist, pos, nrm, margin);
+}
+// does collide_pair send this type pair to MPR (its `default:` case)?  Everything but the analytic routines listed there.
+DI bool is_mpr_pair(int t1, int t2) {
+  switch (t1 * 8 + t2) {
+    case G_PLANE * 8 + G_SPHERE: case G_PLANE * 8 + G_CAPSULE: case G_PLANE * 8 + G_CYLINDER: case G_PLANE * 8 + G_BOX:
+    case G_SPHERE * 8 + G_SPHERE: case G_SPHERE * 8 + G_CAPSULE: case G_SPHERE * 8 + G_BOX:
+    case G_CAPSULE * 8 + G_CAPSULE: case G_CAPSULE * 8 + G_BOX: case G_BOX * 8 + G_BOX: return false;
+    default: return true;
+  }
 }
 
 template <typename T>

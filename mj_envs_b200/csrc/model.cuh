@@ -101,7 +101,9 @@ constexpr int G_LINV = G_JR + CROWS * NVP;       // inverse Cholesky factor of M
 constexpr int G_MINV = G_LINV + NTRI;            // M^-1 (packed)
 constexpr int G_YT = G_MINV + NTRI;              // M^-1 Jt_k^T for the noslip pass [MAXCON][3][NVP]
 constexpr int G_LS = G_YT + MAXCON * 3 * NVP;    // line-search rows of the pyramid edges beyond the register sets (big solve class) [3][6 * MAXCON]: x, y, D
-constexpr int G_DBG = G_LS + 18 * MAXCON;        // debug dump: M packed | qfrc_bias | qfrc_smooth | qacc_smooth | qacc | qfrc_constraint
+constexpr int MPRQ = 32;                          // MPR pairs per env that go through the block-pooled pass of the collide kernel (more: computed in place)
+constexpr int G_MPRRES = G_LS + 18 * MAXCON;     // results of the pooled MPR pass [MPRQ][8]: hit, dist, pos3, nrm3
+constexpr int G_DBG = G_MPRRES + 8 * MPRQ;       // debug dump: M packed | qfrc_bias | qfrc_smooth | qacc_smooth | qacc | qfrc_constraint
 constexpr int G_DBG_M = G_DBG, G_DBG_BIAS = G_DBG + NTRI, G_DBG_QFS = G_DBG_BIAS + NVP, G_DBG_QAS = G_DBG_QFS + NVP,
               G_DBG_QACC = G_DBG_QAS + NVP, G_DBG_QFC = G_DBG_QACC + NVP, G_DBG_XPOS = G_DBG_QFC + NVP,
               G_DBG_XQUAT = G_DBG_XPOS + NBP * 3, G_DBG_EF = G_DBG_XQUAT + NBP * 4;

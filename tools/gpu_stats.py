@@ -10,8 +10,9 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--task", default="hammer")
 ap.add_argument("--n", type=int, default=1024)
 ap.add_argument("--steps", type=int, default=40)
+ap.add_argument("--fp64", action="store_true")
 args = ap.parse_args()
-env = AdroitVecEnv(f"{args.task}-v0", args.n, seed=0, auto_reset=True)
+env = AdroitVecEnv(f"{args.task}-v0", args.n, seed=0, auto_reset=True, fp64=args.fp64)
 L = env.debug_layout()
 env.reset()
 g = torch.Generator(device=env.device); g.manual_seed(0)
@@ -24,4 +25,4 @@ for t in range(args.steps):
 a = np.concatenate(acc)
 for i, name in enumerate(["ncon", "nsimple", "newton iterations", "noslip sweeps"]):
     v = a[:, i]
-    print(f"{args.task} {name:18s} mean {v.mean():6.2f}  p50 {np.percentile(v,50):4.0f} p90 {np.percentile(v,90):4.0f} p99 {np.percentile(v,99):4.0f} max {v.max():4d}   hist {np.bincount(v, minlength=8)[:12]}")
+    print(f"{args.task} {name:18s} mean {v.mean():6.2f}  p50 {np.percentile(v,50):4.0f} p90 {np.percentile(v,90):4.0f} p99 {np.percentile(v,99):4.0f} max {v.max():4d}   hist {np.bincount(v, minlength=8)[:12]} ... last bins {np.bincount(v, minlength=22)[18:22]}")
