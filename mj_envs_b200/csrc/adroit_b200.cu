@@ -56,9 +56,12 @@ struct MapSmooth {
 };
 // the geom frames (written by the smooth kernel) are staged: the broad phase walks ~250 candidate pairs per env and
 // every test starts with two position reads; the kernel is register-bound (2 blocks/SM), shared memory is free
+#ifndef ADROIT_WPB_COLLIDE
+#define ADROIT_WPB_COLLIDE ADROIT_WPB
+#endif
 struct MapCollide {
-  static constexpr int W = WPB;
-  static constexpr int EXTRA = WPB * 16 + WPB * MPRQ * 2;   // per warp: queue length (16-byte slot) + MPRQ 16-bit pair indices
+  static constexpr int W = ADROIT_WPB_COLLIDE;
+  static constexpr int EXTRA = W * 16 + W * MPRQ * 2;   // per warp: queue length (16-byte slot) + MPRQ 16-bit pair indices
   static constexpr int NT = 3, NI = 1;
   static constexpr Reg RT[NT] = {Reg{O_W, 4, 0}, Reg{SM_T + G_GPOS, NGP * 3, R_IN}, Reg{SM_T + G_GMAT, NGP * 9, R_IN}};
   static constexpr Reg RI[NI] = {Reg{I_SURV, MAXSURV / 2, 0}};   // 16-bit entries: 3 blocks/SM stay inside the 32 KB shared-memory carve-out (the kernel lives on L1)
@@ -242,7 +245,7 @@ __global__ void __launch_bounds__(MapSmooth::W * 32) smooth_kernel(const __grid_
 #define ADROIT_COLLIDE_BLOCKS 3   // <= 168 registers: 3 blocks per SM instead of 2 at 202 (collide -11 % hammer, -7.5 % pen; 4 blocks at 128 registers: slower)
 #endif
 template <typename T>
-__global__ void __launch_bounds__(WPB * 32, ADROIT_COLLIDE_BLOCKS) collide_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
+__global__ void __launch_bounds__(MapCollide::W * 32, ADROIT_COLLIDE_BLOCKS) collide_kernel(const __grid_constant__ DModel<T> m, const __grid_constant__ DState<T> st,
                                                             const __grid_constant__ PArgs a) {
   PDL_WAIT()
   // (no early return in this kernel: every warp reaches the two block barriers around the pooled MPR pass)
@@ -964,7 +967,7 @@ int run_t(adroit_sim* s, const DModel<T>& m, const DState<T>& st, int mode, cons
   memset(&a, 0, sizeof a);
   a.debug = debug;
   int nsub = (s->profile || debug) ? 1 : s->nsub;
-  constexpr int EA = WPB * ADROIT_WPB_SOLVE * (ADROIT_WPB_SMOOTH == WPB ? 1 : ADROIT_WPB_SMOOTH);        // sub-batch boundaries fall on block boundaries of every phase kernel
+  constexpr int EA = WPB * ADROIT_WPB_SOLVE * (ADROIT_WPB_SMOOTH == WPB ? 1 : ADROIT_WPB_SMOOTH) * (ADROIT_WPB_COLLIDE % WPB == 0 ? ADROIT_WPB_COLLIDE / WPB : ADROIT_WPB_COLLIDE);        // sub-batch boundaries fall on block boundaries of every phase kernel
   int per = ((st.n + nsub - 1) / nsub + EA - 1) / EA * EA;
   if (per < 64 * WPB) { per = (64 * WPB + EA - 1) / EA * EA; }          // never less than 64 blocks per launch
   nsub = (st.n + per - 1) / per;
