@@ -675,6 +675,19 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
   PR(m.geom_pos, B.reals("geom_pos")); PR(m.geom_mat, gmat); PR(m.geom_size, B.reals("geom_size")); PR(m.geom_rbound, B.reals("geom_rbound"));
   PI(m.site_body, B.ints("site_body")); PI(m.site_par, B.ints("site_par")); PR(m.site_pos, B.reals("site_pos"));
   PI(m.pair_geom, B.ints("pair_geom")); PI(m.pair_condim, B.ints("pair_condim"));
+  {  // packed broad-phase records
+    auto pg = B.ints("pair_geom"), gt = B.ints("geom_type");
+    auto pm = B.reals("pair_margin"), rb = B.reals("geom_rbound");
+    std::vector<int> pw(m.npair);
+    std::vector<double> pb(m.npair);
+    for (int k = 0; k < m.npair; k++) {
+      const int g1 = pg[2 * k], g2 = pg[2 * k + 1];
+      if (g1 > 255 || g2 > 255) throw std::string("geom index beyond the packed pair record");
+      pw[k] = g1 | (g2 << 8) | (gt[g1] << 16) | (gt[g2] << 24);
+      pb[k] = gt[g1] == G_PLANE ? rb[g2] + pm[k] : rb[g1] + rb[g2] + pm[k];
+    }
+    PI(m.pair_word, pw); PR(m.pair_bound, pb);
+  }
   PR(m.pair_friction, B.reals("pair_friction")); PR(m.pair_margin, B.reals("pair_margin"));
   PI(m.tendon_dof, B.ints("tendon_dof")); PI(m.tendon_limited, B.ints("tendon_limited"));
   PR(m.tendon_coef, B.reals("tendon_coef")); PR(m.tendon_range, B.reals("tendon_range")); PR(m.tendon_margin, B.reals("tendon_margin"));

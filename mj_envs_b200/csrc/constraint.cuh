@@ -102,16 +102,16 @@ template <class CX> PHASE_FN int collision_broad(CX& c, unsigned long long* over
     int k = base + c.lane;
     bool hit = false, mpr = false;
     if (k < m.npair) {
-      int g1 = m.pair_geom[2 * k], g2 = m.pair_geom[2 * k + 1];
-      T margin = m.pair_margin[k];
+      const int w = m.pair_word[k];
+      const T bound = m.pair_bound[k];
+      const int g1 = w & 255, g2 = (w >> 8) & 255, t1 = (w >> 16) & 255, t2 = (w >> 24) & 255;
       T dx = gpos[3 * g2] - gpos[3 * g1], dy = gpos[3 * g2 + 1] - gpos[3 * g1 + 1], dz = gpos[3 * g2 + 2] - gpos[3 * g1 + 2];
-      const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
       if (t1 == G_PLANE) {
         const T* R = gmat + 9 * g1;
-        hit = !(dx * R[2] + dy * R[5] + dz * R[8] > m.geom_rbound[g2] + margin);
+        hit = !(dx * R[2] + dy * R[5] + dz * R[8] > bound);
       } else {
-        T bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
         hit = !(dx * dx + dy * dy + dz * dz > bound * bound);
+        const T margin = hit ? m.pair_margin[k] : T(0);
         // second, tighter (still conservative) test: the other geom's bounding sphere against this geom's own shape
         // (large boxes -- table, wall, door -- have bounding spheres that swallow the whole hand)
         T z1[3] = {G.gsize(g1, 0), G.gsize(g1, 1), G.gsize(g1, 2)}, z2[3] = {G.gsize(g2, 0), G.gsize(g2, 1), G.gsize(g2, 2)};

@@ -123,8 +123,8 @@ template <typename T> struct DModel {
   const T *geom_pos, *geom_mat, *geom_size, *geom_rbound;
   const int *site_body, *site_par;
   const T* site_pos;
-  const int *pair_geom, *pair_condim;
-  const T *pair_friction, *pair_margin;
+  const int *pair_geom, *pair_condim, *pair_word;     // pair_word: geom1 | geom2 << 8 | type1 << 16 | type2 << 24 (one load in the broad phase)
+  const T *pair_friction, *pair_margin, *pair_bound;  // pair_bound: rbound1 + rbound2 + margin (plane pairs: rbound2 + margin)
   const int *tendon_dof, *tendon_limited;
   const T *tendon_coef, *tendon_range, *tendon_margin, *tendon_invweight0;
   const int* act_dof;
