@@ -31,10 +31,10 @@ struct RPrim {
 DI bool hit_sphere(const float* o, const float* d, float r, float cz, float& t, float* n) {
   float oz = o[2] - cz, b = o[0] * d[0] + o[1] * d[1] + oz * d[2], c = o[0] * o[0] + o[1] * o[1] + oz * oz - r * r, disc = b * b - c;
   if (disc < 0) return false;
-  float tt = -b - sqrtf(disc);
+  float tt = -b - __fsqrt_rn(disc);
   if (tt <= 1e-4f) return false;
   t = tt;
-  float inv = 1.0f / r;
+  float inv = __fdiv_rn(1.0f, r);
   n[0] = (o[0] + tt * d[0]) * inv; n[1] = (o[1] + tt * d[1]) * inv; n[2] = (oz + tt * d[2]) * inv;
   return true;
 }
@@ -43,7 +43,7 @@ DI bool hit_prim(int type, const float* size, const float* o, const float* d, fl
   t = 3.0e38f;
   if (type == G_PLANE) {
     if (fabsf(d[2]) < 1e-9f) return false;
-    float tt = -o[2] / d[2];
+    float tt = __fdiv_rn(-o[2], d[2]);
     if (tt <= 1e-4f) return false;
     float x = o[0] + tt * d[0], y = o[1] + tt * d[1];
     if ((size[0] > 0 && fabsf(x) > size[0]) || (size[1] > 0 && fabsf(y) > size[1])) return false;
@@ -60,7 +60,7 @@ DI bool hit_prim(int type, const float* size, const float* o, const float* d, fl
       if (fabsf(d[k]) < 1e-12f) {
         if (fabsf(o[k]) > size[k]) return false;
       } else {
-        float inv = 1.0f / d[k], t0 = (-size[k] - o[k]) * inv, t1 = (size[k] - o[k]) * inv, s = -1;
+        float inv = __fdiv_rn(1.0f, d[k]), t0 = (-size[k] - o[k]) * inv, t1 = (size[k] - o[k]) * inv, s = -1;
         if (t0 > t1) { float tmp = t0; t0 = t1; t1 = tmp; s = 1; }
         if (t0 > tn) { tn = t0; ax = k; sg = s; }
         tf = fminf(tf, t1);
@@ -78,10 +78,10 @@ DI bool hit_prim(int type, const float* size, const float* o, const float* d, fl
   if (a > 1e-12f) {
     float disc = b * b - a * c;
     if (disc < 0) return false;   // misses the infinite cylinder: misses caps of either kind too
-    float tt = (-b - sqrtf(disc)) / a, z = o[2] + tt * d[2];
+    float tt = __fdiv_rn(-b - __fsqrt_rn(disc), a), z = o[2] + tt * d[2];
     if (tt > 1e-4f && fabsf(z) <= h) {
       t = tt; found = true;
-      float inv = 1.0f / r;
+      float inv = __fdiv_rn(1.0f, r);
       n[0] = (o[0] + tt * d[0]) * inv; n[1] = (o[1] + tt * d[1]) * inv; n[2] = 0;
     }
   } else if (c > 0) return false;
@@ -94,7 +94,7 @@ DI bool hit_prim(int type, const float* size, const float* o, const float* d, fl
   } else if (fabsf(d[2]) > 1e-12f) {
 #pragma unroll
     for (int s = -1; s <= 1; s += 2) {
-      float tt = (s * h - o[2]) / d[2], x = o[0] + tt * d[0], y = o[1] + tt * d[1];
+      float tt = __fdiv_rn(s * h - o[2], d[2]), x = o[0] + tt * d[0], y = o[1] + tt * d[1];
       if (tt > 1e-4f && tt < t && x * x + y * y <= r * r) { t = tt; n[0] = 0; n[1] = 0; n[2] = (float)s; found = true; }
     }
   }
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_kernel(const __grid_con
     ray_dir(r0 + 2.0f * ty0 + 2 * TH, c0 + 2.0f * tx0 + 2 * TW, dk);
     cost = fminf(cost, dc[0] * dk[0] + dc[1] * dk[1] + dc[2] * dk[2]);
     cost = fmaxf(0.0f, cost - 1e-6f);
-    const float sint = sqrtf(fmaxf(0.0f, 1.0f - cost * cost));
+    const float sint = __fsqrt_rn(fmaxf(0.0f, 1.0f - cost * cost));
     unsigned keep[2];
 #pragma unroll
     for (int q = 0; q < 2; q++) {
@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_kernel(const __grid_con
         if (P.rb2 < 0 || P.vv <= P.rb2) k = true;
         else {
           float invv = rsqrtf(P.vv), cosA = (P.vc[0] * dc[0] + P.vc[1] * dc[1] + P.vc[2] * dc[2]) * invv;
-          float sins = fminf(1.0f, sqrtf(P.rb2) * invv * 1.0001f + 1e-6f), coss = sqrtf(fmaxf(0.0f, 1.0f - sins * sins));
+          float sins = fminf(1.0f, __fsqrt_rn(P.rb2) * invv * 1.0001f + 1e-6f), coss = __fsqrt_rn(fmaxf(0.0f, 1.0f - sins * sins));
           float cossum = cost * coss - sint * sins;                    // cos(tile half-angle + sphere half-angle)
           k = cossum <= 0.0f || cosA >= cossum;
         }
