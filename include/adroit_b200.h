@@ -110,6 +110,20 @@ int adroit_get_solver(adroit_sim* sim, double* qacc_host, int32_t* ncon_host, in
  * counts the episodes in flight.  Synchronises; the caller all-reduces the 4 numbers across ranks. */
 int adroit_reduce_episode(adroit_sim* sim, int flush_running, double* out4_host, void* stream);
 
+/* adroit_reduce_episode for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  NO COUNTERPART IN THE REFERENCE.
+ * Same four statistics as adroit_reduce_episode, but the call allocates nothing, copies nothing to the host and does
+ * not synchronise: it enqueues two kernels on `stream` that leave the result in the CALLER's device buffer
+ * out4_dev (4 x fp64).  The partial sums live in a file-scope `static __device__` array of the library
+ * (ADROIT_NOALLOC_MAX_ENVS / 256 rows of 4 doubles = 8 KB, held by every GPU that loads the library until exit);
+ * a handle with more than ADROIT_NOALLOC_MAX_ENVS envs is rejected with an error, nothing is launched.
+ * The array is shared by EVERY call on a device (all handles, all streams) and keeps the last call's contents; each
+ * call overwrites every row it reads, so nothing has to be cleared, but two calls that overlap on the GPU (different
+ * streams, or graphs replayed concurrently) race on it -- order them.  The sum is taken in a fixed order, so the
+ * result is bit-reproducible; it agrees with adroit_reduce_episode to fp64 rounding of the return sum (counts exact). */
+#define ADROIT_NOALLOC_MAX_ENVS 65536
+int adroit_reduce_episode_noalloc(adroit_sim* sim, int flush_running, double* out4_dev, void* stream);
+
 /* env.render() (hammer_v0.py:177-181 -> HeadlessObserver.render, headless_observer.py:34-52, + PlaNet's 128->64 resize):
  * 64x64 RGB of every env from the reference's free camera, ray-cast against the scene's analytic primitives (no GL on
  * this box; see csrc/render.cuh for what is and is not reproduced).  rgb_dev: u8 [n, 64, 64, 3].  Draws the frames of the

@@ -24,6 +24,7 @@ SYMBOLS = {
     "get_frames": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "get_solver": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     "reduce_episode": (C.c_int, [_VP, C.c_int, _VP, _VP]),
+    "reduce_episode_noalloc": (C.c_int, [_VP, C.c_int, _VP, _VP]),
     "launch_count": (C.c_int64, [_VP]),
     "overflow": (C.c_int, [_VP, _VP, _VP]),
     "render": (C.c_int, [_VP, _VP, _VP]),

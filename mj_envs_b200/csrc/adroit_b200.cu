@@ -504,6 +504,50 @@ __global__ void reduce_kernel(const double* acc, const int* t, const int* ep_goa
   }
 }
 
+// ---- adroit_reduce_episode_noalloc: the same statistics with the partial sums in a file-scope array instead of cudaMalloc'ed memory.
+// One block per NOALLOC_BLOCK envs writes its four partial sums into its own row of the scratch; a second one-block launch adds the rows in a
+// fixed order (the result does not depend on block scheduling, unlike the atomicAdd of reduce_kernel).  Every row a call reads was written by
+// that same call, so nothing in the scratch has to start at zero and the previous call's contents are harmless.
+constexpr int NOALLOC_BLOCK = 256;
+constexpr int NOALLOC_MAX_ENVS = ADROIT_NOALLOC_MAX_ENVS;
+constexpr int NOALLOC_MAX_BLOCKS = NOALLOC_MAX_ENVS / NOALLOC_BLOCK;
+static_assert(NOALLOC_MAX_ENVS % NOALLOC_BLOCK == 0, "ADROIT_NOALLOC_MAX_ENVS must be a multiple of the block size");
+static __device__ __align__(256) double g_noalloc_partials[NOALLOC_MAX_BLOCKS * 4];   // 8 KB per GPU that loads the library, held until exit
+
+__device__ __forceinline__ void block_sum4(double (&v)[4], double (*sh)[32]) {   // result valid in warp 0 (every lane)
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int k = 0; k < 4; k++) v[k] = warp_sum(v[k]);
+  if (lane == 0) for (int k = 0; k < 4; k++) sh[k][warp] = v[k];
+  __syncthreads();
+  if (warp == 0)
+    for (int k = 0; k < 4; k++) v[k] = warp_sum(lane < (int)(blockDim.x >> 5) ? sh[k][lane] : 0.0);
+}
+__global__ void __launch_bounds__(NOALLOC_BLOCK) reduce_partial_kernel(const double* acc, const int* t, const int* ep_goal, const float* retf,
+                                                                       const double* retd, int n, int thr, int flush, double* partials) {
+  __shared__ double sh[4][32];
+  double v[4] = {0, 0, 0, 0};
+  int e = blockIdx.x * NOALLOC_BLOCK + threadIdx.x;
+  if (e < n) {
+    for (int k = 0; k < 4; k++) v[k] = acc[4 * e + k];
+    if (flush && t[e] > 0) {
+      v[0] += retf ? (double)retf[e] : retd[e];
+      v[1] += ep_goal[e] > 0;
+      v[2] += ep_goal[e] > thr;
+      v[3] += 1;
+    }
+  }
+  block_sum4(v, sh);
+  for (int k = 0; k < 4; k++) if (threadIdx.x == k) partials[4 * blockIdx.x + k] = v[k];
+}
+__global__ void __launch_bounds__(NOALLOC_BLOCK) reduce_final_kernel(const double* partials, int nblocks, double* out4) {
+  __shared__ double sh[4][32];
+  double v[4] = {0, 0, 0, 0};
+  for (int b = threadIdx.x; b < nblocks; b += NOALLOC_BLOCK)
+    for (int k = 0; k < 4; k++) v[k] += partials[4 * b + k];
+  block_sum4(v, sh);
+  for (int k = 0; k < 4; k++) if (threadIdx.x == k) out4[k] = v[k];
+}
+
 }  // namespace adroit
 
 
@@ -1274,6 +1318,47 @@ int adroit_reduce_episode(adroit_sim* s, int flush_running, double* out4_host, v
   s->launches++;
   CK(cudaMemcpyAsync(out4_host, s->d_out4, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// Device address of g_noalloc_partials on `device` (which must be current).  In host code the array's name is only a stand-in for the
+// symbol, not a device address: it is resolved once per device with cudaGetSymbolAddress (no allocation) and cached.
+static int noalloc_scratch(int device, double** out) {
+  constexpr int MAXDEV = 64;
+  static double* cache[MAXDEV];          // written once per device with the same value by whichever thread gets there first
+  if (device < 0 || device >= MAXDEV) FAIL("device id %d outside the no-alloc scratch table", device);
+  double* p = __atomic_load_n(&cache[device], __ATOMIC_ACQUIRE);
+  if (!p) {
+    CK(cudaGetSymbolAddress((void**)&p, g_noalloc_partials));
+    if (!p) FAIL("cudaGetSymbolAddress returned a null address for the no-alloc scratch");
+    __atomic_store_n(&cache[device], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return 0;
+}
+
+int adroit_reduce_episode_noalloc(adroit_sim* s, int flush_running, double* out4_dev, void* stream) {
+  if (!s) FAIL("sim is NULL");
+  if (!out4_dev) FAIL("out4_dev is NULL");
+  if (s->n > NOALLOC_MAX_ENVS)
+    FAIL("adroit_reduce_episode_noalloc: %d envs exceed the static scratch (ADROIT_NOALLOC_MAX_ENVS = %d); use adroit_reduce_episode", s->n,
+         NOALLOC_MAX_ENVS);
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaSetDevice(s->device));
+  double* partials = nullptr;
+  if (noalloc_scratch(s->device, &partials)) return 1;
+  int thr = s->task == T_PEN ? 20 : 25;
+  int blocks = (s->n + NOALLOC_BLOCK - 1) / NOALLOC_BLOCK;
+  if (s->f64)
+    reduce_partial_kernel<<<blocks, NOALLOC_BLOCK, 0, st>>>(s->sd.acc, s->sd.t, s->sd.ep_goal, nullptr, s->sd.ep_return, s->n, thr, flush_running,
+                                                            partials);
+  else
+    reduce_partial_kernel<<<blocks, NOALLOC_BLOCK, 0, st>>>(s->sf.acc, s->sf.t, s->sf.ep_goal, s->sf.ep_return, nullptr, s->n, thr, flush_running,
+                                                            partials);
+  CK(cudaGetLastError());
+  reduce_final_kernel<<<1, NOALLOC_BLOCK, 0, st>>>(partials, blocks, out4_dev);
+  CK(cudaGetLastError());
+  s->launches += 2;
   return 0;
 }
 

@@ -247,6 +247,15 @@ class AdroitVecEnv:
             out = allreduce_stats(out, self.device)
         return out
 
+    def reduce_episode_noalloc(self, out4: torch.Tensor, flush_running=False):
+        """The statistics of reduce_episode written into the caller's device tensor `out4` (4 x float64) by
+        adroit_reduce_episode_noalloc: no allocation, no host copy, no synchronisation, no all-reduce (usable under
+        CUDA graph capture; limit ADROIT_NOALLOC_MAX_ENVS = 65536 envs per handle, calls must not overlap on the GPU)."""
+        if out4.dtype != torch.float64 or out4.numel() != 4 or not out4.is_cuda or not out4.is_contiguous():
+            raise ValueError("out4 must be a contiguous CUDA tensor of 4 float64")
+        self.abi.check(self.abi.reduce_episode_noalloc(self._h, int(flush_running), out4.data_ptr(), self._stream()))
+        return out4
+
     # ------------------------------------------------------------------ introspection (parity tests)
     def frames(self):
         n = self.num_envs
