@@ -616,17 +616,24 @@ template <typename T> DI void store_vec(T* x, int n, int lane, T x0, T x1) {
 }
 
 #ifndef ADROIT_BORDERED_SWEEPS
-#define ADROIT_BORDERED_SWEEPS 0   // measured on B200: fewer instructions but a longer dependent chain (border warp sums); 1-2 % slower
+#define ADROIT_BORDERED_SWEEPS 1   // 1: register-row / bordered sweeps below (a third of the instructions of the plain loops, chain = shuffle + FMA per step)
 #endif
 #if ADROIT_BORDERED_SWEEPS
-// Triangular sweeps, bordered: the leading min(n,32) block runs on ONE register per lane (x0 = x[lane]); the 1..4 rows
-// beyond lane 31 (n = 33 hammer, 36 relocate) are a border whose entries every lane keeps redundantly in registers --
-// each border row costs one coalesced row read and (forward sweep) one warp sum, instead of doubling the work of every
-// one of the n column steps for the sake of lanes 0..n-33.
+// Triangular sweeps.  The leading min(n,32) block runs on ONE register per lane (x0 = x[lane]), fully unrolled, with nothing on
+// the dependent chain but one shuffle and one FMA per step:
+//   forward  (column k of L = entry k of every lane's own row): the lane's row is read ONCE into 32 registers (8 vector loads
+//            instead of 32 bank-conflicting scalar ones) and, for SCALE, pre-multiplied by dinv[k], so that the value broadcast in
+//            step k is the lane's running, unscaled x[k];
+//   backward (row k of L is contiguous: one conflict-free load per step, independent of the chain): every lane carries its
+//            entry already multiplied by its own dinv, so that lane k's register IS x[k] when step k broadcasts it.
+// Both rely on what the factorisations leave in the padded rows: ZERO on the diagonal (chol_dense / ltdl_factor store it so; the
+// pivots live in dinv) and zero pads right of it (never written since the allocation).
+// The 1..4 rows beyond lane 31 (n = 33 hammer, 36 relocate) are a border whose entries every lane keeps redundantly in
+// registers: each border row costs one coalesced row read and (forward sweep) one warp sum.
 // for k = n-1..0: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[k][i] * xk for i < k      (row k of L is contiguous)
-template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, const T* dinv, T d0, T d1, T& x0, T& x1, int n, int lane) {
   const unsigned FULL = 0xffffffffu;
-  const int nb = n < 32 ? n : 32;
+  (void)dinv;
   if (n > 32) {
     T xb[4], db[4];
 #pragma unroll
@@ -643,24 +650,41 @@ template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1
     }
     x1 = lane == 0 ? xb[0] : lane == 1 ? xb[1] : lane == 2 ? xb[2] : lane == 3 ? xb[3] : T(0);
   }
-#pragma unroll 4
-  for (int k = nb - 1; k >= 0; k--) {
-    T xk = __shfl_sync(FULL, SCALE ? x0 * d0 : x0, k);
-    if (SCALE && lane == k) x0 = xk;
-    if (lane < k) x0 -= L[rowoff(k) + lane] * xk;
+  // (rows k >= n of the leading block, when n < 32, are zero: their steps change nothing and are not guarded)
+  T u = SCALE ? x0 * d0 : x0;
+#pragma unroll
+  for (int k = 31; k >= 1; k--) {
+    T lk = L[rowoff(k) + lane];              // lanes >= k read the zero diagonal / pads or, beyond the row, a later row: discarded below
+    if (SCALE) lk *= d0;
+    T xk = __shfl_sync(FULL, u, k);
+    if (lane < k) u -= lk * xk;
   }
+  x0 = u;
 }
 // for k = 0..n-1: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[i][k] * xk for i > k      (column k of L: one row per lane)
-template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, const T* dinv, T d0, T d1, T& x0, T& x1, int n, int lane) {
   const unsigned FULL = 0xffffffffu;
-  const int nb = n < 32 ? n : 32;
   const T* r0 = L + rowoff(lane);
-#pragma unroll 4
-  for (int k = 0; k < nb; k++) {
-    T xk = __shfl_sync(FULL, SCALE ? x0 * d0 : x0, k);
-    if (SCALE && lane == k) x0 = xk;
-    if (lane > k && lane < nb) x0 -= r0[k] * xk;
+  T a[32];
+#pragma unroll
+  for (int g = 0; g < 8; g++) {
+    Vec4<T> v;
+    v.v[0] = v.v[1] = v.v[2] = v.v[3] = T(0);
+    if (4 * g <= lane) v = ld4(r0 + 4 * g);  // groups right of the lane's diagonal group belong to later rows
+    if (SCALE) {
+      Vec4<T> dk = ld4(dinv + 4 * g);        // (broadcast read)
+#pragma unroll
+      for (int q = 0; q < 4; q++) v.v[q] *= dk.v[q];
+    }
+#pragma unroll
+    for (int q = 0; q < 4; q++) a[4 * g + q] = v.v[q];
   }
+#pragma unroll
+  for (int k = 0; k < 31; k++) {
+    T xk = __shfl_sync(FULL, x0, k);
+    x0 -= a[k] * xk;                         // a[k] = 0 for k >= lane
+  }
+  if (SCALE) x0 *= d0;
   if (n > 32) {
     T xb[4], db[4];
 #pragma unroll
@@ -681,7 +705,7 @@ template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1,
 }
 #else
 // for k = n-1..0: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[k][i] * xk for i < k      (row k of L is contiguous)
-template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, const T*, T d0, T d1, T& x0, T& x1, int n, int lane) {
 #pragma unroll 2
   for (int k = n - 1; k >= 0; k--) {
     T xs = k < 32 ? x0 : x1;
@@ -694,7 +718,7 @@ template <typename T, bool SCALE> DI void sweep_rows_desc(const T* L, T d0, T d1
   }
 }
 // for k = 0..n-1: xk = x[k] (*dinv[k] if SCALE);  x[i] -= L[i][k] * xk for i > k      (column k of L: one row per lane)
-template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, T d0, T d1, T& x0, T& x1, int n, int lane) {
+template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, const T*, T d0, T d1, T& x0, T& x1, int n, int lane) {
   const T *r0 = L + rowoff(lane), *r1 = L + rowoff(lane + 32);
 #pragma unroll 2
   for (int k = 0; k < n; k++) {
@@ -744,7 +768,7 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
         T d = __shfl_sync(0xffffffffu, a[c], k);
         d = d > tiny<T>() ? d : tiny<T>();
         const T inv = rsqrt_t(d);
-        const T l = lane > k ? a[c] * inv : (lane == k ? d * inv : T(0));
+        const T l = lane > k ? a[c] * inv : T(0);     // (the diagonal is stored as zero: the pivot lives in dinv, the sweeps rely on it)
         T* cb = (c & 1) ? col1 : col0;
         cb[lane] = l;
         if (lane >= k && lane < nb) r0[k] = l;
@@ -779,7 +803,7 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
       T d = __shfl_sync(0xffffffffu, a[k], k);
       d = d > tiny<T>() ? d : tiny<T>();
       const T inv = rsqrt_t(d);
-      const T l = lane > k ? a[k] * inv : (lane == k ? d * inv : T(0));   // lanes above the diagonal sit the column out
+      const T l = lane > k ? a[k] * inv : T(0);   // lanes on and above the diagonal sit the column out (diagonal stored as zero)
       T* cb = (k & 1) ? col1 : col0;
       cb[lane] = l;
       if (lane >= k && lane < nb) r0[k] = l;
@@ -812,7 +836,7 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
     T d = __shfl_sync(0xffffffffu, s0, j);
     d = d > tiny<T>() ? d : tiny<T>();
     T inv = rsqrt_t(d);
-    if (lane == j) { r0[j] = d * inv; dinv[j] = inv; }
+    if (lane == j) { r0[j] = T(0); dinv[j] = inv; }
     else if (lane > j && lane < nb) r0[j] = s0 * inv;
     __syncwarp();
   }
@@ -850,8 +874,8 @@ template <typename T> DI void chol_solve(const T* L, const T* dinv, T* x, int n,
   T x0, x1, d0, d1;
   load_vec(x, n, lane, x0, x1);
   load_vec(dinv, n, lane, d0, d1);
-  sweep_cols_asc<T, true>(L, d0, d1, x0, x1, n, lane);
-  sweep_rows_desc<T, true>(L, d0, d1, x0, x1, n, lane);
+  sweep_cols_asc<T, true>(L, dinv, d0, d1, x0, x1, n, lane);
+  sweep_rows_desc<T, true>(L, dinv, d0, d1, x0, x1, n, lane);
   store_vec(x, n, lane, x0, x1);
   __syncwarp();
 }
@@ -859,7 +883,7 @@ template <typename T> DI void chol_solve(const T* L, const T* dinv, T* x, int n,
 // Tree-sparse factorisation M = L^T D L of a matrix with the sparsity of the joint-space inertia (entry (k,i) non-zero
 // only if i is an ancestor dof of k): eliminating leaves first creates no fill-in (Featherstone; MuJoCo's mj_factorM
 // uses the same order).  One step per dof, its (ancestor, ancestor) pair updates spread over the lanes; the schedule
-// ld_start / ld_pair is built on the host.  On return: strict lower part = L, diagonal = D, dinv = 1/D.
+// ld_start / ld_pair is built on the host.  On return: strict lower part = L, diagonal = 0, dinv = 1/D.
 #ifndef ADROIT_LTDL_LEVEL
 #define ADROIT_LTDL_LEVEL 0   // measured equal to the serial form on B200 (profiles/R2c_ab_lockstep.txt): the chain of ~50 barrier-separated steps is as long as 33 pivots
 #endif
@@ -923,13 +947,15 @@ template <typename T> PHASE_FN void ltdl_factor_serial(const DModel<T>& m, T* A,
     __syncwarp();
     // row k: L[k][i] = A[k][i] / D[k] for every i < k (entries outside the ancestor pattern are zero and stay zero)
     for (int i = lane; i < k; i += 32) A[rowoff(k) + i] = rk[i] * inv;
-    if (lane == 0) dinv[k] = inv;
+    if (lane == 0) { dinv[k] = inv; A[rowoff(k) + k] = T(0); }   // D lives in dinv; the sweeps want a zero diagonal in the rows
     __syncwarp();
   }
 }
 template <typename T> PHASE_FN void ltdl_factor(const DModel<T>& m, T* A, T* dinv, int lane) {
 #if ADROIT_LTDL_LEVEL
   ltdl_factor_lv(m, A, dinv, lane);
+  for (int j = lane; j < m.nv; j += 32) A[tri(j, j)] = T(0);
+  __syncwarp();
 #else
   ltdl_factor_serial(m, A, dinv, lane);
 #endif
@@ -939,9 +965,9 @@ template <typename T> DI void ltdl_solve(const T* L, const T* dinv, T* x, int n,
   T x0, x1, d0, d1;
   load_vec(x, n, lane, x0, x1);
   load_vec(dinv, n, lane, d0, d1);
-  sweep_rows_desc<T, false>(L, d0, d1, x0, x1, n, lane);
+  sweep_rows_desc<T, false>(L, dinv, d0, d1, x0, x1, n, lane);
   x0 *= d0; x1 *= d1;
-  sweep_cols_asc<T, false>(L, d0, d1, x0, x1, n, lane);
+  sweep_cols_asc<T, false>(L, dinv, d0, d1, x0, x1, n, lane);
   store_vec(x, n, lane, x0, x1);
   __syncwarp();
 }
