@@ -1085,10 +1085,64 @@ template <typename T> SUB_FN void symv_range(const T* A, const T* x, T* y, int n
   if (i0 < n) y[i0] = y0;
   if (i1 < n) y[i1] = y1;
 }
+#ifndef ADROIT_FAST_SYMV
+#define ADROIT_FAST_SYMV 1   // fully unrolled on registers (x once into 32 registers, compile-time row offsets): ~230 instructions instead of ~540
+#endif
 template <typename T, bool COMPACT = false, bool SH = false> SUB_FN void symv(const T* A, const T* x, T* y, int n, int lane) {
   __builtin_assume(__isShared(A));
   __builtin_assume(__isShared(x));
   if constexpr (SH) __builtin_assume(__isShared(y));
+#if ADROIT_FAST_SYMV
+  {
+    // Leading 32x32 block: lane i owns y[i].  Relies on zero pads right of the diagonal in the rows of A, on zero rows of A and
+    // zero entries of x at and beyond n (all zero since the allocation / the staging: no loop ever writes them).
+    T xs[32];
+#pragma unroll
+    for (int g = 0; g < 8; g++) {
+      Vec4<T> v = ld4(x + 4 * g);              // (broadcast read)
+#pragma unroll
+      for (int q = 0; q < 4; q++) xs[4 * g + q] = v.v[q];
+    }
+    const T* r0 = A + rowoff(lane);
+    T y0 = 0;
+#pragma unroll
+    for (int g = 0; g < 8; g++) {              // row part: sum_{k <= i} A[i][k] x[k]
+      if (4 * g <= lane) {
+        Vec4<T> a = ld4(r0 + 4 * g);
+        y0 += a.v[0] * xs[4 * g] + a.v[1] * xs[4 * g + 1] + a.v[2] * xs[4 * g + 2] + a.v[3] * xs[4 * g + 3];
+      }
+    }
+#pragma unroll
+    for (int j = 1; j < 32; j++) {             // transpose part: row j contributes A[j][i] x[j] to every i < j (row j is contiguous)
+      T aj = A[rowoff(j) + lane];
+      if (lane < j) y0 += aj * xs[j];
+    }
+    if (n > 32) {
+      const T xl = x[lane];
+      Vec4<T> xv = ld4(x + 32);
+      T yb[4] = {T(0), T(0), T(0), T(0)};
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        if (32 + q < n) {                      // warp-uniform
+          const T* row = A + rowoff(32 + q);
+          const T aq = row[lane];
+          y0 += aq * xv.v[q];
+          T sq = warp_sum(aq * xl);
+#pragma unroll
+          for (int p = 0; p < 4; p++) {
+            if (p <= q) sq += row[32 + p] * xv.v[p];
+            else if (32 + p < n) sq += A[rowoff(32 + p) + 32 + q] * xv.v[p];
+          }
+          yb[q] = sq;
+        }
+      }
+      const T y1 = lane == 0 ? yb[0] : lane == 1 ? yb[1] : lane == 2 ? yb[2] : yb[3];
+      if (lane + 32 < n) y[lane + 32] = y1;
+    }
+    if (lane < n) y[lane] = y0;
+    return;
+  }
+#endif
   T y0 = 0, y1 = 0;
   const int i0 = lane, i1 = lane + 32;
   if constexpr (COMPACT) {
