@@ -516,11 +516,11 @@ static __device__ __align__(256) double g_noalloc_partials[NOALLOC_MAX_BLOCKS * 
 
 __device__ __forceinline__ void block_sum4(double (&v)[4], double (*sh)[32]) {   // result valid in warp 0 (every lane)
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int k = 0; k < 4; k++) v[k] = warp_sum(v[k]);
-  if (lane == 0) for (int k = 0; k < 4; k++) sh[k][warp] = v[k];
+  _Pragma("unroll") for (int k = 0; k < 4; k++) v[k] = warp_sum(v[k]);
+  if (lane == 0) { _Pragma("unroll") for (int k = 0; k < 4; k++) sh[k][warp] = v[k]; }
   __syncthreads();
   if (warp == 0)
-    for (int k = 0; k < 4; k++) v[k] = warp_sum(lane < (int)(blockDim.x >> 5) ? sh[k][lane] : 0.0);
+    _Pragma("unroll") for (int k = 0; k < 4; k++) v[k] = warp_sum(lane < (int)(blockDim.x >> 5) ? sh[k][lane] : 0.0);
 }
 __global__ void __launch_bounds__(NOALLOC_BLOCK) reduce_partial_kernel(const double* acc, const int* t, const int* ep_goal, const float* retf,
                                                                        const double* retd, int n, int thr, int flush, double* partials) {
@@ -528,7 +528,7 @@ __global__ void __launch_bounds__(NOALLOC_BLOCK) reduce_partial_kernel(const dou
   double v[4] = {0, 0, 0, 0};
   int e = blockIdx.x * NOALLOC_BLOCK + threadIdx.x;
   if (e < n) {
-    for (int k = 0; k < 4; k++) v[k] = acc[4 * e + k];
+    _Pragma("unroll") for (int k = 0; k < 4; k++) v[k] = acc[4 * e + k];
     if (flush && t[e] > 0) {
       v[0] += retf ? (double)retf[e] : retd[e];
       v[1] += ep_goal[e] > 0;
@@ -537,15 +537,15 @@ __global__ void __launch_bounds__(NOALLOC_BLOCK) reduce_partial_kernel(const dou
     }
   }
   block_sum4(v, sh);
-  for (int k = 0; k < 4; k++) if (threadIdx.x == k) partials[4 * blockIdx.x + k] = v[k];
+  _Pragma("unroll") for (int k = 0; k < 4; k++) if (threadIdx.x == k) partials[4 * blockIdx.x + k] = v[k];
 }
 __global__ void __launch_bounds__(NOALLOC_BLOCK) reduce_final_kernel(const double* partials, int nblocks, double* out4) {
   __shared__ double sh[4][32];
   double v[4] = {0, 0, 0, 0};
   for (int b = threadIdx.x; b < nblocks; b += NOALLOC_BLOCK)
-    for (int k = 0; k < 4; k++) v[k] += partials[4 * b + k];
+    _Pragma("unroll") for (int k = 0; k < 4; k++) v[k] += partials[4 * b + k];
   block_sum4(v, sh);
-  for (int k = 0; k < 4; k++) if (threadIdx.x == k) out4[k] = v[k];
+  _Pragma("unroll") for (int k = 0; k < 4; k++) if (threadIdx.x == k) out4[k] = v[k];
 }
 
 }  // namespace adroit
