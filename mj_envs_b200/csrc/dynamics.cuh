@@ -759,16 +759,22 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
 #pragma unroll
     for (int q = 0; q < 4; q++) a[4 * g + q] = v.v[q];
   }
+  // Pivot look-ahead: the next pivot A[k+1][k+1] - L[k+1][k]^2 needs nothing but lane k+1's own multiplier, so it is formed and
+  // broadcast BEFORE the column goes through shared memory -- the dependent chain of a column is pivot -> rsqrt -> multiplier ->
+  // FMA -> shuffle instead of ... -> store -> barrier -> load -> FMA -> shuffle (the kernel is latency-bound, profiles/R2g_*).
+  // Same operands, same FMA as the regular update of that entry: bit-identical factor.
+  T dnext = __shfl_sync(0xffffffffu, a[0], 0);
 #pragma unroll 1
   for (int k0 = 0; k0 < nb; k0 += 4) {
 #pragma unroll
     for (int c = 0; c < 4; c++) {
       const int k = k0 + c;
       if (k < nb) {                                 // warp-uniform
-        T d = __shfl_sync(0xffffffffu, a[c], k);
+        T d = dnext;
         d = d > tiny<T>() ? d : tiny<T>();
         const T inv = rsqrt_t(d);
         const T l = lane > k ? a[c] * inv : T(0);     // (the diagonal is stored as zero: the pivot lives in dinv, the sweeps rely on it)
+        dnext = __shfl_sync(0xffffffffu, a[c + 1] - l * l, (k + 1) & 31);
         T* cb = (c & 1) ? col1 : col0;
         cb[lane] = l;
         if (lane >= k && lane < nb) r0[k] = l;
