@@ -818,6 +818,7 @@ template <typename T> void fill_model(DModel<T>& m, Arena& A, const Blob& B) {
     }
     PI(m.tri_abk, tri_abk);
     PI(m.ld_start, ld_start); PI(m.ld_pair, ld_pair); PI(m.wl_pair, wl_pair); PI(m.tri_ab, tri_ab);
+    for (int i = 0; i < NVP + 4; i++) m.ld_start_v[i] = ld_start[i <= nv ? i : nv];
     if (maxd > MAXDEPTH) throw std::string("dof ancestor chain longer than dynamics.cuh's MAXDEPTH");
     std::vector<int> anc_tab((size_t)nv * MAXDEPTH, -1);
     for (int k = 0; k < nv; k++)

@@ -929,9 +929,7 @@ template <typename T> PHASE_FN void ltdl_factor_serial(const DModel<T>& m, T* A,
   const int n = m.nv;
   // schedule words (host-built): packed offset of A[i][j] | i << 10 | j << 16.  The first pass of the NEXT pivot's
   // words is fetched while the current pivot is eliminated: no model-table load on the chain of the 33 serial pivots.
-  // (the pivot start offsets sit in two registers per lane, so the prefetch address is one shuffle away)
-  const int ls0 = lane <= n ? m.ld_start[lane] : 0, ls1 = lane + 32 <= n ? m.ld_start[lane + 32] : 0;
-  auto start = [&](int k) { return k < 32 ? __shfl_sync(0xffffffffu, ls0, k) : __shfl_sync(0xffffffffu, ls1, k - 32); };
+  auto start = [&](int k) { return m.ld_start_v[k]; };   // (by value in the kernel parameters: a uniform constant-bank read)
   int beg = start(n - 1), end = start(n);
   int nxt = beg + lane < end ? m.ld_pair[beg + lane] : 0;
   for (int k = n - 1; k >= 0; k--) {
@@ -989,47 +987,40 @@ constexpr int MAXDEPTH = 14;   // longest dof ancestor chain (relocate: 6 arm + 
 template <typename T> PHASE_FN void minv_tree(const DModel<T>& m, T* L, const T* dinv, int* par, T* Minv, int lane) {
   const unsigned FULL = 0xffffffffu;
   const int nv = m.nv;
-  T w[2][MAXDEPTH];
-#pragma unroll
-  for (int pass = 0; pass < 2; pass++) {
+  // One rolled pass per 32 rows, rows 32.. FIRST: their chains read rows below 32 (still L) and each other (all reads of a pass
+  // come before its writes), while the rows below 32 never read a row at or beyond 32 -- so the unrolled chain code exists once.
+#pragma unroll 1
+  for (int pass = nv > 32 ? 1 : 0; pass >= 0; pass--) {
     const int k = lane + 32 * pass;
     const bool act = k < nv;
-    if (pass == 1 && nv <= 32) break;                 // warp-uniform
     if (act) par[k] = m.dof_parent[k];
     const int d = act ? m.dof_depth[k] : 0;
     const int maxd = __reduce_max_sync(FULL, d);
     const int* an = m.anc_tab + (act ? k : 0) * MAXDEPTH;
-    const T* rk = L + rowoff(act ? k : 0);
+    T* rk = L + rowoff(act ? k : 0);
+    T w[MAXDEPTH];
     int j[MAXDEPTH], ro[MAXDEPTH];
 #pragma unroll
     for (int t = 0; t < MAXDEPTH; t++) {
-      j[t] = 0; ro[t] = 0; w[pass][t] = 0;
+      j[t] = 0; ro[t] = 0; w[t] = 0;
       if (t < maxd) {                                 // warp-uniform
         j[t] = t < d ? an[t] : 0;
         ro[t] = rowoff(j[t]);
         T acc = rk[j[t]];
 #pragma unroll
-        for (int q = 0; q < t; q++) acc += w[pass][q] * L[ro[q] + j[t]];
-        w[pass][t] = t < d ? -acc : T(0);
+        for (int q = 0; q < t; q++) acc += w[q] * L[ro[q] + j[t]];
+        w[t] = t < d ? -acc : T(0);
       }
     }
-  }
-  __syncwarp();
-#pragma unroll
-  for (int pass = 0; pass < 2; pass++) {
-    const int k = lane + 32 * pass;
-    if (pass == 1 && nv <= 32) break;
-    if (k < nv) {
-      const int d = m.dof_depth[k];
-      const int* an = m.anc_tab + k * MAXDEPTH;
-      T* rk = L + rowoff(k);
+    __syncwarp();
+    if (act) {
 #pragma unroll
       for (int t = 0; t < MAXDEPTH; t++)
-        if (t < d) rk[an[t]] = w[pass][t];
+        if (t < d) rk[j[t]] = w[t];
       rk[k] = T(1);
     }
+    __syncwarp();
   }
-  __syncwarp();
   // (a, b, lca(a,b)) packed in one table word, fetched one pass ahead: the model-table load is off the dependent chain
   int nxt = lane < m.n_tri ? m.tri_abk[lane] : 0;
   for (int p = lane; p < m.n_tri; p += 32) {

@@ -141,6 +141,7 @@ template <typename T> struct DModel {
   // fixed-tendon tables by value: kernel-parameter (constant-bank) reads instead of L2 round trips on the row loops' chain
   int n_lvitems;
   int lv_steps[MAXLVSTEP];                           // step s: type (0 pivots, 1 updates, 2 row scaling, 3 end) | first item << 2; it ends where step s+1 starts
+  int ld_start_v[NVP + 4];                           // ld_start by value: the pivot loop of ltdl_factor reads it with a uniform index (constant bank)
   int tdof[2 * MAXTENDON];
   T tcoef[2 * MAXTENDON];
   T par0[NPARP];
