@@ -241,6 +241,12 @@ __global__ void __launch_bounds__(MapSmooth::W * 32) smooth_kernel(const __grid_
 }
 
 // ---------------------------------------------------------------- phase 2: collision
+#ifndef ADROIT_MPR_SPREAD
+#define ADROIT_MPR_SPREAD 3
+#endif
+#ifndef ADROIT_MPR_SPREAD_MIN
+#define ADROIT_MPR_SPREAD_MIN 4    // measured: 2 costs hammer +8 % of its collide kernel, 8 and beyond lose pen's -4.7 %
+#endif
 #ifndef ADROIT_COLLIDE_BLOCKS
 #define ADROIT_COLLIDE_BLOCKS 3   // <= 168 registers: 3 blocks per SM instead of 2 at 202 (collide -11 % hammer, -7.5 % pen; 4 blocks at 128 registers: slower)
 #endif
@@ -275,8 +281,27 @@ __global__ void __launch_bounds__(MapCollide::W * 32, ADROIT_COLLIDE_BLOCKS) col
     off[0] = 0;
 #pragma unroll
     for (int w = 0; w < MAP::W; w++) off[w + 1] = off[w] + qn[4 * w];
+    // which queued pair a thread takes: 0 = thread e takes pair e (the first warps fill up, the others idle through the pass),
+    // 1 = the queue cut into one contiguous chunk per warp, 2 = dealt round-robin over the warps.  A warp's MPR time is set by the
+    // divergence among its lanes as much as by its longest pair, so fewer pairs per warp on more warps is the shorter pass.
+#if ADROIT_MPR_SPREAD == 1
+    const int total_ = off[MAP::W], chunk_ = (total_ + MAP::W - 1) / MAP::W;
+    for (int i_ = lane; i_ < chunk_; i_ += 32) {
+      const int e = warp * chunk_ + i_;
+      if (e >= total_) break;
+      int w = 0;
+#elif ADROIT_MPR_SPREAD == 2
+    for (int e = lane * MAP::W + warp; e < off[MAP::W]; e += MAP::W * 32) {
+      int w = 0;
+#elif ADROIT_MPR_SPREAD == 3
+    // up to a warp's worth of pairs stays on the first warp (the others wait at the barrier without touching the MPR code: hammer,
+    // a handful of pairs per block), more is dealt round-robin over the warps (pen: 40-60 pairs per block)
+    for (int e = off[MAP::W] <= ADROIT_MPR_SPREAD_MIN ? (int)threadIdx.x : lane * MAP::W + warp; e < off[MAP::W]; e += MAP::W * 32) {
+      int w = 0;
+#else
     for (int e = threadIdx.x; e < off[MAP::W]; e += MAP::W * 32) {
       int w = 0;
+#endif
 #pragma unroll
       for (int q = 1; q < MAP::W; q++) w += e >= off[q];
       const int j = e - off[w];
