@@ -744,7 +744,10 @@ template <typename T, bool SCALE> DI void sweep_cols_asc(const T* L, const T*, T
 #ifndef ADROIT_REG_CHOL
 #define ADROIT_REG_CHOL 2
 #endif
-template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, int n, int lane) {
+#ifndef ADROIT_CHOL_BORDER_INLOOP
+#define ADROIT_CHOL_BORDER_INLOOP 1
+#endif
+template <typename T, int NBORD> DI void chol_dense_impl(T* A, T* dinv, T* col0, T* col1, int n, int lane) {
   const int nb = n < 32 ? n : 32;
   T* r0 = A + rowoff(lane);
 #if ADROIT_REG_CHOL == 2
@@ -764,12 +767,21 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
   // FMA -> shuffle instead of ... -> store -> barrier -> load -> FMA -> shuffle (the kernel is latency-bound, profiles/R2h_*).
   // Same operands, same FMA as the regular update of that entry: bit-identical factor.
   T dnext = __shfl_sync(0xffffffffu, a[0], 0);
+#if ADROIT_CHOL_BORDER_INLOOP
+  // Rows 32..n-1 ride along: lane j holds A[32+q][j]; at column k lane k's entry times 1/L[k][k] IS L[32+q][k], which is broadcast
+  // and folded into the entries right of it with the lanes' own multipliers -- three instructions per column and border row, none of
+  // them on the pivot chain, instead of a 32-step forward substitution per border row after the factorisation (a third of the
+  // factorisation's latency for hammer's single row, more than half for relocate's four).
+  T bq[4];
+#pragma unroll
+  for (int q = 0; q < 4; q++) bq[q] = (q < NBORD && 32 + q < n) ? A[rowoff(32 + q) + lane] : T(0);
+#endif
 #pragma unroll 1
   for (int k0 = 0; k0 < nb; k0 += 4) {
 #pragma unroll
     for (int c = 0; c < 4; c++) {
       const int k = k0 + c;
-      if (k < nb) {                                 // warp-uniform
+      if (NBORD > 0 || k < nb) {                    // warp-uniform; with border rows n > 32 and every column exists: no branch at all
         T d = dnext;
         d = d > tiny<T>() ? d : tiny<T>();
         const T inv = rsqrt_t(d);
@@ -779,6 +791,15 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
         cb[lane] = l;
         if (lane >= k && lane < nb) r0[k] = l;
         if (lane == k) dinv[k] = inv;
+#if ADROIT_CHOL_BORDER_INLOOP
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          if (q < NBORD) {                          // compile-time: no branch, no reconvergence bookkeeping in the column loop
+            const T lb = __shfl_sync(0xffffffffu, bq[q] * inv, k);
+            bq[q] = lane == k ? lb : (lane > k ? bq[q] - lb * l : bq[q]);
+          }
+        }
+#endif
         __syncwarp();
 #pragma unroll
         for (int g = 0; g < 8; g++) {
@@ -847,8 +868,15 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
     __syncwarp();
   }
 #endif
+#if ADROIT_CHOL_BORDER_INLOOP && ADROIT_REG_CHOL == 2
+#pragma unroll
+  for (int q = 0; q < 4; q++)
+    if (q < NBORD && 32 + q < n) A[rowoff(32 + q) + lane] = bq[q];
+  __syncwarp();
+#endif
   for (int r = 32; r < n; r++) {
     T* rr = A + rowoff(r);
+#if !(ADROIT_CHOL_BORDER_INLOOP && ADROIT_REG_CHOL == 2)
     T x = rr[lane], dl = dinv[lane];
 #pragma unroll 4
     for (int k = 0; k < 32; k++) {          // L11 y = a
@@ -858,6 +886,7 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
     }
     rr[lane] = x;
     __syncwarp();
+#endif
     for (int q = 32; q <= r; q++) {
       const T* rq = A + rowoff(q);
       T p = rr[lane] * rq[lane];
@@ -874,6 +903,16 @@ template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, 
       __syncwarp();
     }
   }
+}
+// (one instance per border-row count the four tasks have: 0 door / pen, 1 hammer, 4 relocate and anything in between)
+template <typename T> PHASE_FN void chol_dense(T* A, T* dinv, T* col0, T* col1, int n, int lane) {
+#if ADROIT_CHOL_BORDER_INLOOP && ADROIT_REG_CHOL == 2
+  if (n <= 32) chol_dense_impl<T, 0>(A, dinv, col0, col1, n, lane);
+  else if (n == 33) chol_dense_impl<T, 1>(A, dinv, col0, col1, n, lane);
+  else chol_dense_impl<T, 4>(A, dinv, col0, col1, n, lane);
+#else
+  chol_dense_impl<T, 0>(A, dinv, col0, col1, n, lane);
+#endif
 }
 // x <- (L L^T)^-1 x  (x in shared memory)
 template <typename T> DI void chol_solve(const T* L, const T* dinv, T* x, int n, int lane) {
