@@ -764,7 +764,7 @@ template <typename T, int NBORD> DI void chol_dense_impl(T* A, T* dinv, T* col0,
   }
   // Pivot look-ahead: the next pivot A[k+1][k+1] - L[k+1][k]^2 needs nothing but lane k+1's own multiplier, so it is formed and
   // broadcast BEFORE the column goes through shared memory -- the dependent chain of a column is pivot -> rsqrt -> multiplier ->
-  // FMA -> shuffle instead of ... -> store -> barrier -> load -> FMA -> shuffle (the kernel is latency-bound, profiles/R2h_*).
+  // FMA -> shuffle instead of ... -> store -> barrier -> load -> FMA -> shuffle (the kernel is latency-bound, profiles/R2i_*).
   // Same operands, same FMA as the regular update of that entry: bit-identical factor.
   T dnext = __shfl_sync(0xffffffffu, a[0], 0);
 #if ADROIT_CHOL_BORDER_INLOOP
